@@ -1,0 +1,432 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 frame path.
+
+Metric (BASELINE.json): 1080p BGR24 frames/s, whole job, and achieved HBM GB/s vs the measured peak.
+Default workload = BASELINE.json configs[1]: 16 synthetic 1080p yuv420p cameras per GPU, one step =
+one tick = ONE batched kernel launch converting all 16 frames.  Under torchrun every rank owns its
+own 16 cameras on its own GPU (weak scaling, no data-path collective); times are max over ranks.
+
+One JSON line on rank 0:
+  value        frames/s with the decoded planes already resident in HBM (kernel-only, CUDA events on
+               the launching stream, K steps back to back, inputs rotate over buffer sets > L2)
+  e2e          frames/s through the public API with HOST buffers: FramePath.submit (pinned staging) ->
+               tick (H2D, kernel, D2H) -> result_packed, copies inside the timed region
+  roofline     algorithmic bytes (4.5 B/px) per launch / measured launch duration vs MEASURED_PEAKS.json
+  cpu_baseline the reference's CPU path (libswscale sws_scale + tobytes, read_image.py:94-97) timed on
+               this box's host cores on a bounded sample of the same frames
+`--impl reference` prints the CPU arm alone in the same shape (rank 0 only under torchrun).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "1080p_bgr24_frames_per_sec"
+UNIT = "frames/s"
+ALG_BYTES_PER_PX = 4.5          # 1.5 B/px read (Y + U/4 + V/4) + 3 B/px written
+FALLBACK_HBM_GBS = 6650.0       # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
+
+WORKLOADS = {
+    # name: (cameras per GPU, fmt, w, h, description)
+    "16x1080p": (16, "yuv420p", 1920, 1080, "16 synthetic 1080p yuv420p cameras per GPU, one batched launch per tick (BASELINE configs[1])"),
+    "8x1080p": (8, "yuv420p", 1920, 1080, "8 synthetic 1080p yuv420p cameras per GPU (BASELINE configs[2] layout: 64 cameras over 8 GPUs)"),
+    "8x4k-nv12": (8, "nv12", 3840, 2160, "8 synthetic 3840x2160 NV12 cameras per GPU (BASELINE configs[3] frames)"),
+    "1x480p": (1, "yuv420p", 640, 480, "one 640x480 yuv420p stream (BASELINE configs[0])"),
+}
+
+
+# ------------------------------------------------------------------------------------------------
+# rank plumbing (gloo on CPU in tests, nccl on the box)
+# ------------------------------------------------------------------------------------------------
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def cameras_for_rank(workload: str, rank: int, world: int):
+    """Static partition: rank r owns cameras [r*n, (r+1)*n) — disjoint sets, no exchange step."""
+    n, fmt, w, h, _ = WORKLOADS[workload]
+    return [dict(camera=rank * n + i, fmt=fmt, w=w, h=h, seed=rank * n + i) for i in range(n)]
+
+
+def _reduce(value: float, op, device: str):
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        return float(value)
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=op)
+    return float(t.item())
+
+
+def max_over_ranks(value: float, device: str = "cuda") -> float:
+    import torch.distributed as dist
+    return _reduce(value, dist.ReduceOp.MAX, device)
+
+
+def sum_over_ranks(value: float, device: str = "cuda") -> float:
+    import torch.distributed as dist
+    return _reduce(value, dist.ReduceOp.SUM, device)
+
+
+def barrier():
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        dist.barrier()
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks (NVML in-process; nvidia-smi fallback)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index: int, period_s: float = 0.004):
+        self.samples = []   # (t, sm_mhz, reasons_mask, power_w)
+        self.period = period_s
+        self._stop = threading.Event()
+        self._thr = None
+        self.sm_max = None
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # honour CUDA_VISIBLE_DEVICES ordering when it is a plain index list
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = index
+            if vis:
+                try:
+                    phys = int(vis.split(",")[index])
+                except Exception:
+                    phys = index
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # pragma: no cover
+            self.err = str(e)
+
+    def _run(self):
+        nv, h = self._nv, self._h
+        while not self._stop.is_set():
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                try:
+                    rs = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                try:
+                    pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
+                except Exception:
+                    pw = 0.0
+                self.samples.append((time.perf_counter(), sm, rs, pw))
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def start(self):
+        if self.ok:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr:
+            self._thr.join(timeout=1)
+
+    def summary(self, windows):
+        """windows: list of (t0, t1) perf_counter intervals that were under load."""
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "note": "NVML unavailable"}
+        sel = [s for s in self.samples if any(a <= s[0] <= b for a, b in windows)]
+        note = "sampled inside the timed regions"
+        if not sel:
+            sel, note = self.samples, "timed regions shorter than the sampling period; all samples of the run"
+        mask = 0
+        for s in sel:
+            mask |= s[2]
+        reasons = [n for b, n in self.REASONS.items() if mask & b and n != "gpu_idle"]
+        return {"sm_mhz": statistics.median(s[1] for s in sel) if sel else None, "sm_max_mhz": self.sm_max,
+                "reasons": reasons, "samples": len(sel), "power_w_max": round(max((s[3] for s in sel), default=0.0), 1),
+                "note": note}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own path on host cores (libswscale via the oracle binding)
+# ------------------------------------------------------------------------------------------------
+def cpu_frames_per_sec(cams, steps: int, warmup: int, threads: int, with_tobytes: bool = True):
+    """Each step converts one frame of every camera (the same tick the GPU arm converts), spread
+    over `threads` host threads; ctypes releases the GIL inside sws_scale.  Returns (fps, seconds)."""
+    from oracle import swscale_live as live   # bench.py's CPU leg is allowed to execute oracle/
+    from video_edge_ai_proxy_b200.synth import make_planes
+    if not live.available():
+        raise RuntimeError("bundled libswscale not found")
+    threads = max(1, min(threads, len(cams)))
+    convs = []
+    for c in cams:
+        cv = live.Converter(c["fmt"], c["w"], c["h"])
+        cv.load(make_planes(c["fmt"], c["w"], c["h"], c["seed"]))
+        convs.append(cv)
+
+    def one(cv):
+        cv.scale()                                   # frame.to_ndarray(format='bgr24')  read_image.py:94
+        if with_tobytes:
+            return cv.result().nbytes                # one H*W*3 copy = np.ndarray.tobytes(img)  :97
+        return 0
+
+    with ThreadPoolExecutor(threads) as pool:
+        for _ in range(warmup):
+            list(pool.map(one, convs))
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            list(pool.map(one, convs))
+        dt = time.perf_counter() - t0
+    for cv in convs:
+        cv.close()
+    return steps * len(cams) / dt, dt
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except Exception:
+        pass
+    return "unknown"
+
+
+def run_reference(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return 0
+    n, fmt, w, h, desc = WORKLOADS[args.workload]
+    cams = cameras_for_rank(args.workload, 0, 1)
+    T = host_threads()
+    try:
+        fps, dt = cpu_frames_per_sec(cams, args.steps, args.warmup, T, with_tobytes=True)
+    except Exception as e:
+        print(json.dumps({"impl": "reference", "unavailable": str(e)[:200]}))
+        return 0
+    used = min(T, len(cams))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": round(fps, 2), "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 4),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {desc}", "frames_per_step": len(cams),
+                   "cpu": cpu_model(), "note": "host cores only; the reference has no GPU path"},
+        "cpu_baseline": {"value": round(fps, 2), "unit": UNIT, "cores": used, "kind": "reference",
+                         "sample": f"{args.steps} ticks x {len(cams)} frames {w}x{h} {fmt}: libswscale 9.1.100 sws_scale "
+                                   f"(SWS_BILINEAR, the call PyAV makes for read_image.py:94) + tobytes (:97), "
+                                   f"{used} threads of {T} available"},
+        "e2e": {"value": round(fps, 2), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    from video_edge_ai_proxy_b200 import FramePath, desc_from_tensors, make_meta
+    from video_edge_ai_proxy_b200.synth import make_planes
+
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the GPU arm has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+
+    n, fmt, w, h, desc = WORKLOADS[args.workload]
+    cams = cameras_for_rank(args.workload, rank, world)
+    frame_alg_bytes = int(ALG_BYTES_PER_PX * w * h)
+    per_set_bytes = n * frame_alg_bytes
+    l2_bytes = torch.cuda.get_device_properties(dev).L2_cache_size
+    n_sets = max(args.sets, 2, -(-3 * l2_bytes // per_set_bytes))   # footprint of the rotation >= 3x L2
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    path = FramePath(local_rank)
+
+    # ---- resident inputs: n_sets copies of every camera's planes, separate outputs per set ----------
+    host_planes = [make_planes(c["fmt"], c["w"], c["h"], c["seed"]) for c in cams]
+    plans, outs = [], []
+    for s in range(n_sets):
+        descs, set_outs = [], []
+        for c, hp in zip(cams, host_planes):
+            planes = [torch.from_numpy(p).to(dev) for p in hp]
+            out = torch.empty((c["h"], c["w"], 3), dtype=torch.uint8, device=dev)
+            descs.append(desc_from_tensors(c["fmt"], planes, out))
+            set_outs.append((planes, out))
+        plans.append(path.plan(descs))
+        outs.append(set_outs)
+    stream = torch.cuda.current_stream(dev)
+    sptr = stream.cuda_stream
+
+    for i in range(max(args.warmup, 3)):
+        plans[i % n_sets].launch(sptr)
+    torch.cuda.synchronize(dev)
+    # every set must hold the same, non-trivial result (same inputs): the kernel really ran everywhere
+    ref_sum = [int(o.sum(dtype=torch.int64).item()) for _, o in outs[0]]
+    for s in range(1, n_sets):
+        got = [int(o.sum(dtype=torch.int64).item()) for _, o in outs[s]]
+        if got != ref_sum or min(got) == 0:
+            raise SystemExit(f"bench.py: buffer set {s} disagrees with set 0 — refusing to time a broken kernel")
+
+    # ---- value: K steps, device-timed on the launching stream ---------------------------------------
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    torch.cuda.synchronize(dev)
+    w0 = time.perf_counter()
+    e0.record(stream)
+    for i in range(args.steps):
+        plans[i % n_sets].launch(sptr)
+    e1.record(stream)
+    torch.cuda.synchronize(dev)
+    w1 = time.perf_counter()
+    barrier()
+    dev_ms = e0.elapsed_time(e1)
+    dev_ms = max_over_ranks(dev_ms) if world > 1 else dev_ms
+    total_frames = sum_over_ranks(n) if world > 1 else n
+    value = total_frames * args.steps / (dev_ms / 1e3)
+    launch_ms = dev_ms / args.steps
+    achieved = plans[0].alg_bytes / (launch_ms / 1e3) / 1e9      # this rank's GPU (all ranks run the same plan)
+    peak, peak_src = measured_peak()
+
+    for p in plans:
+        p.close()
+    del outs, plans
+    torch.cuda.empty_cache()
+
+    # ---- e2e: host planes -> submit -> tick -> packed VideoFrame in pinned memory --------------------
+    e2e_steps = max(3, min(args.steps, args.e2e_steps))
+    names = [f"cam{c['camera']}" for c in cams]
+    for name, c in zip(names, cams):
+        path.open_stream(name, c["fmt"], c["w"], c["h"], memory_buffer=1)
+    meta = make_meta(timestamp=1604660000123, pts=900000, dts=897000, time_base=1 / 90000, is_keyframe=True, frame_type="I", keyframe=1)
+    pool = ThreadPoolExecutor(min(len(cams), host_threads()))
+
+    def submit_all():
+        list(pool.map(lambda a: path.submit(a[0], a[1], meta), zip(names, host_planes)))
+
+    def consume():
+        tot = 0
+        for name in names:
+            tot += len(path.result_packed(name))      # the message a producer hands to XADD
+        return tot
+
+    for _ in range(3):
+        submit_all(); path.tick(); consume()
+    barrier()
+    torch.cuda.synchronize(dev)
+    x0 = time.perf_counter()
+    submit_all(); path.tick_begin()
+    for i in range(1, e2e_steps):
+        submit_all(); path.tick_begin()               # H2D of tick i overlaps D2H of tick i-1
+        path.tick_wait(); consume()
+    path.tick_wait(); msg_bytes = consume()
+    torch.cuda.synchronize(dev)
+    x1 = time.perf_counter()
+    barrier()
+    e2e_s = max_over_ranks(x1 - x0) if world > 1 else (x1 - x0)
+    e2e_value = total_frames * e2e_steps / e2e_s
+    st = path.stats()
+    h2d_per_step = st["h2d_bytes"] // max(st["ticks"], 1)
+    d2h_per_step = st["d2h_bytes"] // max(st["ticks"], 1)
+    pool.shutdown()
+    sampler.stop()
+    clocks = sampler.summary([(w0, w1), (x0, x1)])
+    path.close()
+
+    line = {
+        "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": round(launch_ms, 5), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: {desc}", "frames_per_step_per_gpu": n, "format": fmt, "width": w, "height": h,
+                   "l2": f"inputs/outputs rotate over {n_sets} buffer sets of {per_set_bytes / 1e6:.0f} MB (> {l2_bytes / 1e6:.0f} MB L2)",
+                   "parallelism": f"cameras sharded {n}/GPU, no collective", "store_mode": os.environ.get("VEP_STORE_MODE", "0")},
+        "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+                     "traffic": None, "peak_source": peak_src, "frac_of_nominal_8TBs": round(achieved / 8000.0, 4),
+                     "alg_bytes_per_launch": per_set_bytes, "kernel": "vep::yuv_to_bgr24_batched"},
+        "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d_per_step), "d2h_bytes_per_step": int(d2h_per_step),
+                "steps": e2e_steps, "api": "FramePath.submit (host planes -> pinned staging) + tick_begin/tick_wait (2 ticks in flight) + result_packed",
+                "pcie_gbs": round((h2d_per_step + d2h_per_step) * e2e_steps / e2e_s / 1e9, 2), "message_bytes": msg_bytes},
+        "gpu_launches": args.steps,
+        "clocks": clocks,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        T = host_threads()
+        try:
+            # bounded sample: ~20 s of CPU work in total, spread over the host threads
+            est_ms = 1.6 * (w * h) / (1920 * 1080)
+            cpu_steps = max(3, int(20000 / (est_ms * n)))
+            fps, dt = cpu_frames_per_sec(cams, cpu_steps, 2, T, with_tobytes=True)
+            fps_scale, _ = cpu_frames_per_sec(cams, max(3, cpu_steps // 4), 1, T, with_tobytes=False)
+            used = min(T, len(cams))
+            line["cpu_baseline"] = {"value": round(fps, 1), "unit": UNIT, "cores": used, "kind": "reference",
+                                    "sample": f"{cpu_steps} ticks x {n} frames {w}x{h} {fmt} ({dt:.1f} s wall): libswscale 9.1.100 sws_scale "
+                                              f"(what PyAV calls for read_image.py:94) + tobytes (:97) on {used} threads of {T}; "
+                                              f"sws_scale alone: {fps_scale:.0f} frames/s; cpu: {cpu_model()}"}
+        except Exception as e:
+            line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {e}"}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5000)
+    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="16x1080p", choices=sorted(WORKLOADS))
+    ap.add_argument("--sets", type=int, default=9, help="minimum number of rotating buffer sets")
+    ap.add_argument("--e2e-steps", type=int, default=60)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        # the CPU arm times one tick per step as well; cap so the run ends within minutes
+        return run_reference(args)
+    return run_gpu(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

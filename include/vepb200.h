@@ -1,0 +1,160 @@
+/* vepb200.h — C ABI of the B200 frame path (libvepb200.so).
+ *
+ * Drop-in boundary for ONE path of tangtang888/video-edge-ai-proxy: the conversion of a decoded
+ * YUV 4:2:0 frame to packed BGR24 and its packing into the `VideoFrame` message, i.e. reference
+ * python/read_image.py:94-119.  The reference has no FFI seam there (it calls PyAV, which calls
+ * libswscale); each entry point below cites the reference lines whose work it takes over.
+ * Everything is plain C: pointers, sizes, ints.  No torch / CUDA types appear in a signature
+ * (CUDA streams travel as `void*`).
+ *
+ * Conventions: every function returns 0 on success or a negative vep_status; the text of the
+ * last error of the calling thread is available from vep_last_error().  Nothing here calls
+ * abort()/exit().  There is no CPU fallback: without a usable CUDA device vep_create fails.
+ */
+#ifndef VEPB200_H
+#define VEPB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VEP_ABI_VERSION 1
+
+typedef enum {
+    VEP_OK = 0,
+    VEP_ERR_INVALID_ARG = -1,   /* null pointer, bad id, bad enum */
+    VEP_ERR_GEOMETRY = -2,      /* odd width/height, stride < row bytes, nv12 with height < 8 */
+    VEP_ERR_CUDA = -3,          /* a CUDA runtime call failed; see vep_last_error() */
+    VEP_ERR_NOMEM = -4,
+    VEP_ERR_STATE = -5,         /* call out of order (e.g. result before any tick) */
+    VEP_ERR_NO_FRAME = -6,      /* nothing converted yet for this stream */
+    VEP_ERR_BUSY = -7           /* too many ticks in flight / slot still in use */
+} vep_status;
+
+/* Pixel formats a decoder hands over (PyAV `frame.format.name` at read_image.py:94). */
+typedef enum {
+    VEP_FMT_YUV420P = 0,   /* planar, limited (MPEG) range  — swscale coefficient set 1 */
+    VEP_FMT_YUVJ420P = 1,  /* planar, full (JPEG) range     — swscale coefficient set 2 */
+    VEP_FMT_NV12 = 2       /* Y plane + interleaved UV, limited range */
+} vep_pixfmt;
+
+/* One frame of a batched conversion, all pointers in DEVICE memory.
+ * Takes the place of one `frame.to_ndarray(format='bgr24')` call (read_image.py:94):
+ * plane[]/stride[] are the AVFrame planes and linesizes, dst is the (H, W, 3) uint8 result
+ * (dst_stride = 3*width for the contiguous array PyAV returns after its padding strip). */
+typedef struct {
+    const uint8_t *plane[3]; /* Y,U,V  (nv12: Y,UV,NULL) */
+    int32_t stride[3];       /* bytes per row of each plane */
+    uint8_t *dst;            /* B,G,R interleaved */
+    int32_t dst_stride;      /* bytes per output row, >= 3*width */
+    int32_t width, height;   /* both even; nv12 needs height >= 8 */
+    int32_t fmt;             /* vep_pixfmt */
+    int32_t convert;         /* 0: the decode gate skipped this frame (read_image.py:80), no work */
+} vep_frame_desc;
+
+/* Per-frame scalars copied into the VideoFrame message (read_image.py:101-111). */
+typedef struct {
+    int64_t timestamp;   /* field 4: frame.time*time_base.denominator, else wall-clock ms (:89-91) */
+    int64_t pts;         /* field 6 */
+    int64_t dts;         /* field 7 */
+    int64_t packet;      /* field 13: index of the packet inside its GOP (:107) */
+    int64_t keyframe;    /* field 14: running GOP counter (:108) */
+    double time_base;    /* field 10 */
+    int32_t is_keyframe; /* field 5 — of the packet last popped from the queue (:110) */
+    int32_t is_corrupt;  /* field 9 (:111) */
+    char frame_type[8];  /* field 8: pict_type.name, NUL-terminated ("I","P","B",…) */
+} vep_frame_meta;
+
+typedef struct vep_ctx vep_ctx;   /* one per GPU; owns streams, staging, device buffers */
+typedef struct vep_plan vep_plan; /* a validated, device-resident batch of frame descriptors */
+
+/* ---- library ------------------------------------------------------------------------------ */
+int vep_abi_version(void);
+const char *vep_last_error(void);
+const char *vep_status_name(int status);
+
+/* ---- context (replaces "one container per camera", rtsp_process_manager.go:106-111, with one
+ *      context per GPU serving many camera streams) ------------------------------------------- */
+int vep_create(int device, vep_ctx **out);
+void vep_destroy(vep_ctx *ctx);
+
+/* ---- device-resident batched conversion (read_image.py:94 for N frames at once) -------------
+ * Descriptors hold device pointers (e.g. torch tensors' data_ptr()).  One kernel launch converts
+ * every descriptor with convert != 0.  `cuda_stream` is a cudaStream_t (NULL = default stream).
+ * vep_convert_batch validates, uploads the table and launches; a plan does the first two once
+ * so a fixed camera set costs one launch per tick. */
+int vep_convert_batch(vep_ctx *ctx, const vep_frame_desc *descs, int n, void *cuda_stream);
+int vep_plan_create(vep_ctx *ctx, const vep_frame_desc *descs, int n, vep_plan **out);
+int vep_plan_launch(vep_plan *plan, void *cuda_stream);
+/* frames with convert!=0, CTAs per launch, algorithmic bytes (4.5*W*H per converted frame) */
+int vep_plan_info(const vep_plan *plan, int *n_converted, int *n_ctas, int64_t *alg_bytes);
+void vep_plan_destroy(vep_plan *plan);
+
+/* ---- host pipeline: camera streams, pinned staging, tick (read_image.py:87-121) --------------
+ * stream_open declares a camera (device_id in the reference) with a fixed decoded geometry.
+ * `ring_depth` mirrors --memory_buffer / XADD MAXLEN (read_image.py:121): a result stays valid
+ * until `ring_depth` newer frames of that stream have been converted (minimum 2 slots are kept). */
+int vep_stream_open(vep_ctx *ctx, int stream_id, int fmt, int width, int height, int ring_depth);
+int vep_stream_close(vep_ctx *ctx, int stream_id);
+
+/* Hand one decoded frame (HOST pointers: AVFrame planes + linesizes) to the library.  The planes
+ * are copied into pinned staging before the call returns, so the caller's frame may be freed.
+ * convert == 0 records a gate-skipped frame (counted, never copied).  Callable concurrently for
+ * different streams; one producer per stream. */
+int vep_submit(vep_ctx *ctx, int stream_id, const uint8_t *const plane[3], const int32_t stride[3],
+               const vep_frame_meta *meta, int convert);
+/* Zero-copy variant: get pointers into the next pinned staging slot (a decoder can write its
+ * planes there directly), then commit it. */
+int vep_acquire_input(vep_ctx *ctx, int stream_id, uint8_t *plane_out[3], int32_t stride_out[3]);
+int vep_commit_input(vep_ctx *ctx, int stream_id, const vep_frame_meta *meta);
+
+/* One tick: for every stream with a committed frame — H2D on that camera's CUDA stream, ONE
+ * batched kernel launch over all of them, D2H into the pinned output ring.  vep_tick is
+ * begin+wait.  At most 2 ticks may be in flight (begin, begin, wait, …) so H2D of tick t+1
+ * overlaps D2H of tick t. */
+int vep_tick_begin(vep_ctx *ctx, int *n_frames);
+int vep_tick_wait(vep_ctx *ctx);
+int vep_tick(vep_ctx *ctx, int *n_frames);
+
+/* Newest converted frame of a stream: pointer to H*W*3 contiguous BGR bytes in pinned host
+ * memory (what `np.ndarray.tobytes(img)` yields at read_image.py:97) and shape = {H, W, 3}
+ * (img.shape, :95). */
+int vep_result(vep_ctx *ctx, int stream_id, const uint8_t **bgr, size_t *len, int32_t shape[3]);
+/* Same frame as the complete serialized VideoFrame (vf.SerializeToString(), read_image.py:119;
+ * schema proto/video_streaming.proto:78-93) — header and trailer are written around the payload
+ * in the same pinned buffer, so the pointer can go to XADD (:121) without another copy. */
+int vep_result_packed(vep_ctx *ctx, int stream_id, const uint8_t **msg, size_t *len);
+/* Older results of the same stream: age 0 is the newest, age k the k-th before it (a catch-up
+ * burst, read_image.py:81-85, converts several frames of one camera in one tick).  Guaranteed for
+ * age < ring_depth; frames of the tick just waited for are all still there (up to ring_depth+3)
+ * until the stream is fed again. */
+int vep_result_packed_at(vep_ctx *ctx, int stream_id, int age, const uint8_t **msg, size_t *len);
+int vep_result_at(vep_ctx *ctx, int stream_id, int age, const uint8_t **bgr, size_t *len, int32_t shape[3]);
+/* Device-side view of the same result for GPU consumers (zero-copy; valid like vep_result). */
+int vep_result_device(vep_ctx *ctx, int stream_id, const uint8_t **bgr_dev, int32_t shape[3]);
+
+/* ---- VideoFrame wire framing alone (read_image.py:99-119 minus the payload copy) -------------
+ * Writes the bytes that precede and follow `data` in the serialized message.  prefix needs
+ * >= 32 bytes, suffix >= 192 bytes.  shape is {height, width, 3}. */
+int vep_videoframe_frame(const vep_frame_meta *meta, int32_t width, int32_t height,
+                         uint8_t *prefix, int32_t *prefix_len, uint8_t *suffix,
+                         int32_t *suffix_len);
+
+/* ---- counters (the reference only prints) -------------------------------------- */
+typedef struct {
+    int64_t frames_offered;   /* submits incl. gate-skipped */
+    int64_t frames_converted;
+    int64_t ticks;
+    int64_t kernel_launches;
+    int64_t h2d_bytes, d2h_bytes;
+    float last_kernel_ms;     /* device time of the most recent tick's kernel (CUDA events) */
+} vep_stats;
+int vep_get_stats(vep_ctx *ctx, vep_stats *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VEPB200_H */

@@ -1,0 +1,219 @@
+"""GPU: parity of the sm_100a kernels, called through the C ABI, against the oracle and the goldens."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+from oracle import formulas as F  # noqa: E402
+from oracle import swscale_live as L  # noqa: E402
+from video_edge_ai_proxy_b200 import FramePath, VepError, desc_from_device_ptrs, desc_from_tensors  # noqa: E402
+from video_edge_ai_proxy_b200 import _abi  # noqa: E402
+from video_edge_ai_proxy_b200.synth import exhaustive_yuv_frame, make_planes  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def path():
+    if not torch.cuda.is_available():
+        pytest.fail("marked gpu but no CUDA device")
+    p = FramePath(0)
+    yield p
+    p.close()
+
+
+def gpu_convert(path, fmt, planes, out=None, stream=None):
+    t = [torch.from_numpy(np.ascontiguousarray(p)).cuda() for p in planes]
+    h, w = planes[0].shape
+    if out is None:
+        out = torch.full((h, w, 3), 0xA5, dtype=torch.uint8, device="cuda")
+    path.convert_batch([desc_from_tensors(fmt, t, out)], torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    return out.cpu().numpy()
+
+
+def _digest(a):
+    return int(a.sum(dtype=np.int64)), hashlib.sha256(a.tobytes()).hexdigest()
+
+
+def test_golden_table_every_simd_row(path, golden_pixels):
+    for r in golden_pixels["rows"]:
+        if r["path"] != "simd":
+            continue
+        out = gpu_convert(path, r["fmt"], make_planes(r["fmt"], r["w"], r["h"], r["seed"]))
+        assert _digest(out) == (r["sum"], r["sha256"]), r
+
+
+def test_small_fixtures(path, small_frames):
+    for fmt, w, h, seed, planes, want in small_frames:
+        assert np.array_equal(gpu_convert(path, fmt, planes), want), (fmt, w, h)
+
+
+def test_exhaustive_yuv_triples_planar_both_ranges(path):
+    planes = exhaustive_yuv_frame()
+    for fmt in ("yuv420p", "yuvj420p"):
+        got = gpu_convert(path, fmt, planes)
+        # oracle in 512-row bands to bound memory
+        for r0 in range(0, 4096, 512):
+            want = F.to_bgr24(fmt, (planes[0][r0:r0 + 512], planes[1][r0 // 2:r0 // 2 + 256], planes[2][r0 // 2:r0 // 2 + 256]))
+            assert np.array_equal(got[r0:r0 + 512], want), (fmt, r0)
+
+
+@pytest.mark.parametrize("fmt", ["yuv420p", "yuvj420p", "nv12"])
+def test_seeded_random_config_sizes(path, fmt):
+    for (w, h) in ((640, 480), (1280, 720), (1920, 1080), (3840, 2160)):
+        for seed in (1, 2):
+            planes = make_planes(fmt, w, h, seed)
+            assert np.array_equal(gpu_convert(path, fmt, planes), F.to_bgr24(fmt, planes)), (fmt, w, h, seed)
+
+
+@pytest.mark.parametrize("fmt", ["yuv420p", "yuvj420p", "nv12"])
+def test_ragged_geometries_take_the_generic_path(path, fmt):
+    for w in (2, 6, 14, 18, 30, 34, 62, 130, 510, 514, 642, 1922):
+        for h in (2, 4, 8, 10, 18, 50):
+            if fmt == "nv12" and h < 8:
+                continue
+            planes = make_planes(fmt, w, h, 31 * w + h)
+            assert np.array_equal(gpu_convert(path, fmt, planes), F.to_bgr24(fmt, planes)), (fmt, w, h)
+
+
+@pytest.mark.parametrize("fmt", ["yuv420p", "nv12"])
+def test_fast_path_widths_and_partial_segments(path, fmt):
+    # multiples of 16 around the 512-px segment boundary: full, partial and single-lane segments
+    for w in (16, 32, 496, 512, 528, 1008, 1024, 1040, 2048, 4096):
+        planes = make_planes(fmt, w, 16, w)
+        assert np.array_equal(gpu_convert(path, fmt, planes), F.to_bgr24(fmt, planes)), (fmt, w)
+
+
+def test_live_libswscale_agrees_on_the_box(path):
+    if not L.available():
+        pytest.skip("bundled libswscale not found")
+    assert L.on_simd_path()
+    for fmt, w, h in (("yuv420p", 1920, 1080), ("yuvj420p", 640, 480), ("nv12", 1280, 720), ("yuv420p", 50, 6)):
+        planes = make_planes(fmt, w, h, 77)
+        assert np.array_equal(gpu_convert(path, fmt, planes), L.to_bgr24(fmt, planes, w, h)), (fmt, w, h)
+
+
+def test_padded_strides_and_unaligned_pointers(path):
+    rng = np.random.default_rng(5)
+    for fmt, w, h, pad, off in (("yuv420p", 1920, 64, 64, 0), ("yuv420p", 640, 32, 48, 16), ("yuv420p", 640, 32, 7, 3),
+                                ("nv12", 640, 32, 32, 0), ("nv12", 640, 32, 10, 2), ("yuvj420p", 320, 16, 0, 1)):
+        planes = make_planes(fmt, w, h, 9)
+        dev, ptrs, strides = [], [], []
+        for p in planes:
+            ph, pw = p.shape
+            buf = torch.from_numpy(rng.integers(0, 256, (ph * (pw + pad) + off + 64,), dtype=np.uint8)).cuda()
+            view = buf[off:off + ph * (pw + pad)].view(ph, pw + pad)
+            view[:, :pw] = torch.from_numpy(p).cuda()
+            dev.append(buf)
+            ptrs.append(view.data_ptr())
+            strides.append(pw + pad)
+        dstride = 3 * w + (pad // 16) * 16 if off == 0 else 3 * w + pad
+        obuf = torch.full((h * dstride + off + 64,), 0x5A, dtype=torch.uint8, device="cuda")
+        d = desc_from_device_ptrs(fmt, w, h, ptrs, strides, obuf.data_ptr() + off, dstride)
+        path.convert_batch([d], torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        o = obuf.cpu().numpy()
+        rows = o[off:off + h * dstride].reshape(h, dstride)
+        assert np.array_equal(rows[:, :3 * w].reshape(h, w, 3), F.to_bgr24(fmt, planes)), (fmt, w, h, pad, off)
+        # nothing outside the visible W*3 bytes of each row is written (swscale overwrites padding; we must not)
+        assert (rows[:, 3 * w:] == 0x5A).all() and (o[:off] == 0x5A).all() and (o[off + h * dstride:] == 0x5A).all()
+
+
+def test_heterogeneous_batch_one_launch_with_skips(path):
+    specs = [("yuv420p", 640, 480, 1, True), ("nv12", 1280, 720, 2, True), ("yuv420p", 1920, 1080, 3, False),
+             ("yuvj420p", 642, 482, 4, True), ("yuv420p", 1920, 1080, 5, True), ("nv12", 50, 10, 6, True)]
+    descs, keep = [], []
+    for fmt, w, h, seed, conv in specs:
+        planes = make_planes(fmt, w, h, seed)
+        t = [torch.from_numpy(p).cuda() for p in planes]
+        out = torch.full((h, w, 3), 0x11, dtype=torch.uint8, device="cuda")
+        descs.append(desc_from_tensors(fmt, t, out, convert=conv))
+        keep.append((fmt, planes, t, out, conv))
+    before = path.stats()["kernel_launches"]
+    plan = path.plan(descs)
+    assert plan.n_converted == 5
+    assert plan.alg_bytes == sum(int(4.5 * w * h) for _, w, h, _, c in specs if c)
+    plan.launch(torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert path.stats()["kernel_launches"] == before + 1
+    for fmt, planes, t, out, conv in keep:
+        if conv:
+            assert np.array_equal(out.cpu().numpy(), F.to_bgr24(fmt, planes)), fmt
+        else:
+            assert (out == 0x11).all()      # gate-skipped frame: untouched
+    plan.close()
+
+
+def test_linearity_free_properties_at_full_size(path):
+    """Size-independent checks at 16 x 1080p: per-frame independence and determinism."""
+    frames = [make_planes("yuv420p", 1920, 1080, s) for s in range(16)]
+    descs, outs = [], []
+    for pl in frames:
+        t = [torch.from_numpy(p).cuda() for p in pl]
+        out = torch.empty((1080, 1920, 3), dtype=torch.uint8, device="cuda")
+        descs.append(desc_from_tensors("yuv420p", t, out))
+        outs.append((t, out))
+    plan = path.plan(descs)
+    plan.launch(torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    batch = [o.cpu().numpy().copy() for _, o in outs]
+    for i in (0, 7, 15):
+        assert np.array_equal(batch[i], F.to_bgr24("yuv420p", frames[i]))
+    plan.launch(torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    for i, (_, o) in enumerate(outs):
+        assert np.array_equal(o.cpu().numpy(), batch[i])
+    # gray input (U = V = 128) gives B = G = R everywhere
+    Y = frames[0][0]
+    C = np.full((540, 960), 128, np.uint8)
+    g = gpu_convert(path, "yuv420p", (Y, C, C))
+    assert (g[..., 0] == g[..., 1]).all() and (g[..., 1] == g[..., 2]).all()
+    plan.close()
+
+
+def test_all_store_modes_bit_identical():
+    planes = make_planes("yuv420p", 1920, 1080, 42)
+    want = F.to_bgr24("yuv420p", planes)
+    nv = make_planes("nv12", 1040, 64, 43)
+    want_nv = F.to_bgr24("nv12", nv)
+    old = os.environ.get("VEP_STORE_MODE")
+    try:
+        for mode in ("0", "1", "2"):
+            os.environ["VEP_STORE_MODE"] = mode
+            with FramePath(0) as p:
+                assert np.array_equal(gpu_convert(p, "yuv420p", planes), want), mode
+                assert np.array_equal(gpu_convert(p, "nv12", nv), want_nv), mode
+    finally:
+        if old is None:
+            os.environ.pop("VEP_STORE_MODE", None)
+        else:
+            os.environ["VEP_STORE_MODE"] = old
+
+
+def test_rejections(path):
+    planes = make_planes("yuv420p", 64, 16, 0)
+    t = [torch.from_numpy(p).cuda() for p in planes]
+    out = torch.empty((16, 64, 3), dtype=torch.uint8, device="cuda")
+    good = desc_from_tensors("yuv420p", t, out)
+    for mutate, status in ((lambda d: setattr(d, "width", 63), _abi.VEP_ERR_GEOMETRY),
+                           (lambda d: setattr(d, "height", 15), _abi.VEP_ERR_GEOMETRY),
+                           (lambda d: setattr(d, "fmt", 9), _abi.VEP_ERR_INVALID_ARG),
+                           (lambda d: setattr(d, "dst_stride", 100), _abi.VEP_ERR_GEOMETRY),
+                           (lambda d: setattr(d, "dst", 0), _abi.VEP_ERR_INVALID_ARG)):
+        d = desc_from_tensors("yuv420p", t, out)
+        mutate(d)
+        with pytest.raises(VepError) as e:
+            path.convert_batch([good, d])
+        assert e.value.status == status
+    nv = make_planes("nv12", 16, 8, 0)
+    tn = [torch.from_numpy(p).cuda() for p in nv]
+    d = desc_from_tensors("nv12", tn, torch.empty((8, 16, 3), dtype=torch.uint8, device="cuda"))
+    d.height = 6
+    with pytest.raises(VepError) as e:
+        path.convert_batch([d])
+    assert e.value.status == _abi.VEP_ERR_GEOMETRY
+    path.convert_batch([])          # empty batch is fine

@@ -1,0 +1,259 @@
+"""GPU: host pipeline through the C ABI — pinned staging, tick, result ring, packed VideoFrame,
+producer loop with the decode gate and a fake Redis."""
+import threading
+from fractions import Fraction
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+from oracle import formulas as F  # noqa: E402
+from oracle import videoframe_wire as W  # noqa: E402
+from video_edge_ai_proxy_b200 import (CameraControl, FramePath, FrameProducer, VepError, make_meta,  # noqa: E402
+                                      to_ndarray_bgr24)
+from video_edge_ai_proxy_b200 import _abi  # noqa: E402
+from video_edge_ai_proxy_b200.synth import make_planes  # noqa: E402
+
+
+@pytest.fixture()
+def path():
+    if not torch.cuda.is_available():
+        pytest.fail("marked gpu but no CUDA device")
+    p = FramePath(0)
+    yield p
+    p.close()
+
+
+def test_to_ndarray_drop_in(path):
+    for fmt, w, h in (("yuv420p", 640, 480), ("yuvj420p", 1280, 720), ("nv12", 1920, 1080), ("yuv420p", 50, 6)):
+        planes = make_planes(fmt, w, h, 3)
+        img = to_ndarray_bgr24(path, fmt, planes)
+        assert img.dtype == np.uint8 and img.shape == (h, w, 3) and img.flags["C_CONTIGUOUS"]
+        assert np.array_equal(img, F.to_bgr24(fmt, planes))
+
+
+def test_submit_with_decoder_strides(path):
+    """AVFrame planes arrive with linesize > width; the staging copy strips it."""
+    w, h = 1920, 1080
+    Y, U, V = make_planes("yuv420p", w, h, 8)
+    big = [np.zeros((p.shape[0], p.shape[1] + 64), np.uint8) for p in (Y, U, V)]
+    for b, p in zip(big, (Y, U, V)):
+        b[:, :p.shape[1]] = p
+        b[:, p.shape[1]:] = 0xEE
+    path.open_stream("cam", "yuv420p", w, h)
+    path.submit("cam", [b[:, :p.shape[1]] for b, p in zip(big, (Y, U, V))])
+    assert path.tick() == 1
+    assert np.array_equal(path.result("cam"), F.to_bgr24("yuv420p", (Y, U, V)))
+
+
+def test_tick_batches_many_cameras_in_one_launch(path):
+    cams = [(f"c{i}", fmt, w, h, i) for i, (fmt, w, h) in enumerate(
+        [("yuv420p", 1920, 1080)] * 4 + [("nv12", 1280, 720)] * 3 + [("yuvj420p", 640, 480)] * 3 + [("yuv420p", 642, 482)])]
+    for name, fmt, w, h, seed in cams:
+        path.open_stream(name, fmt, w, h)
+        path.submit(name, make_planes(fmt, w, h, seed))
+    s0 = path.stats()
+    assert path.tick() == len(cams)
+    s1 = path.stats()
+    assert s1["kernel_launches"] - s0["kernel_launches"] == 1
+    assert s1["frames_converted"] - s0["frames_converted"] == len(cams)
+    assert s1["h2d_bytes"] > 0 and s1["d2h_bytes"] == sum(w * h * 3 for _, _, w, h, _ in cams)
+    for name, fmt, w, h, seed in cams:
+        assert np.array_equal(path.result(name), F.to_bgr24(fmt, make_planes(fmt, w, h, seed))), name
+    assert path.tick() == 0      # nothing staged -> no launch
+    assert path.stats()["kernel_launches"] == s1["kernel_launches"]
+
+
+def test_packed_videoframe_is_the_reference_message(path):
+    w, h = 640, 480
+    planes = make_planes("yuv420p", w, h, 21)
+    fields = dict(timestamp=1604660000123, pts=-3003, dts=897000, packet=4, keyframe=17, time_base=1 / 90000,
+                  is_keyframe=True, is_corrupt=False, frame_type="I")
+    path.open_stream("cam", "yuv420p", w, h)
+    path.submit("cam", planes, make_meta(**fields))
+    path.tick()
+    msg = bytes(path.result_packed("cam"))
+    bgr = F.to_bgr24("yuv420p", planes)
+    want = W.serialize_videoframe(width=w, height=h, data=bgr.tobytes(), shape=(h, w, 3), **fields)
+    assert msg == want
+    assert msg == W.serialize_with_protobuf_runtime(width=w, height=h, data=bgr.tobytes(), shape=(h, w, 3), **fields)
+    # consumer side, examples/opencv_display.py:48-53
+    VideoFrame, _ = W.dynamic_message_class()
+    vf = VideoFrame()
+    vf.ParseFromString(msg)
+    img = np.frombuffer(vf.data, dtype=np.uint8).reshape([d.size for d in vf.shape.dim])
+    assert np.array_equal(img, bgr) and [d.name for d in vf.shape.dim] == ["0", "1", "2"] and vf.device_id == ""
+
+
+def test_result_ring_semantics(path):
+    w, h = 64, 16
+    path.open_stream("cam", "yuv420p", w, h, memory_buffer=3)
+    with pytest.raises(VepError) as e:
+        path.result("cam")
+    assert e.value.status == _abi.VEP_ERR_NO_FRAME
+    views = []
+    for s in range(3):
+        path.submit("cam", make_planes("yuv420p", w, h, s), make_meta(packet=s))
+        path.tick()
+        views.append(path.result("cam"))
+    # the three newest results are all still valid and distinct buffers
+    for s in range(3):
+        assert np.array_equal(views[s], F.to_bgr24("yuv420p", make_planes("yuv420p", w, h, s)))
+        assert np.array_equal(path.result("cam", age=2 - s), views[s])
+    # a burst of three frames in one tick (catch-up, read_image.py:81-85): all retrievable, oldest first
+    for s in (10, 11, 12):
+        path.submit("cam", make_planes("yuv420p", w, h, s), make_meta(packet=s))
+    assert path.tick() == 3
+    for age, s in ((2, 10), (1, 11), (0, 12)):
+        assert np.array_equal(path.result("cam", age=age), F.to_bgr24("yuv420p", make_planes("yuv420p", w, h, s)))
+    # producer outrunning the ticks is refused, not overwritten
+    with pytest.raises(VepError) as e:
+        for s in range(20):
+            path.submit("cam", make_planes("yuv420p", w, h, s))
+    assert e.value.status == _abi.VEP_ERR_BUSY
+    path.tick()
+
+
+def test_two_ticks_in_flight_and_zero_copy_staging(path):
+    w, h = 1280, 720
+    path.open_stream("cam", "nv12", w, h)
+    frames = [make_planes("nv12", w, h, s) for s in range(4)]
+    got = []
+    for i, pl in enumerate(frames):
+        dst = path.acquire_input("cam")
+        for d, p in zip(dst, pl):
+            d[...] = p
+        path.commit_input("cam", make_meta(packet=i))
+        assert path.tick_begin() == 1
+        if i >= 1:
+            path.tick_wait()
+            got.append(path.result("cam").copy())
+    path.tick_wait()
+    got.append(path.result("cam").copy())
+    with pytest.raises(VepError):
+        path.tick_begin(); path.tick_begin(); path.tick_begin()
+    for g, pl in zip(got, frames):
+        assert np.array_equal(g, F.to_bgr24("nv12", pl))
+
+
+def test_concurrent_producers_one_thread_per_camera(path):
+    n, w, h = 8, 1280, 720
+    for i in range(n):
+        path.open_stream(f"c{i}", "yuv420p", w, h)
+    planes = [make_planes("yuv420p", w, h, 100 + i) for i in range(n)]
+    errs = []
+
+    def prod(i):
+        try:
+            path.submit(f"c{i}", planes[i], make_meta(packet=i))
+        except Exception as e:  # pragma: no cover
+            errs.append(e)
+
+    th = [threading.Thread(target=prod, args=(i,)) for i in range(n)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs
+    assert path.tick() == n
+    for i in range(n):
+        assert np.array_equal(path.result(f"c{i}"), F.to_bgr24("yuv420p", planes[i]))
+
+
+def test_device_result_is_zero_copy_torch_tensor(path):
+    w, h = 640, 480
+    planes = make_planes("yuv420p", w, h, 5)
+    path.open_stream("cam", "yuv420p", w, h)
+    path.submit("cam", planes)
+    path.tick()
+    t = path.result_tensor("cam")
+    assert t.is_cuda and t.dtype == torch.uint8 and tuple(t.shape) == (h, w, 3)
+    assert np.array_equal(t.cpu().numpy(), F.to_bgr24("yuv420p", planes))
+
+
+def test_stream_errors(path):
+    with pytest.raises(VepError):
+        path.open_stream("x", "yuv420p", 641, 480)
+    with pytest.raises(VepError):
+        path.open_stream("x", "nv12", 640, 6)
+    with pytest.raises(VepError):
+        path.open_stream("x", "rgb24", 640, 480)
+    path.open_stream("x", "yuv420p", 640, 480)
+    with pytest.raises(VepError):
+        path.open_stream("x", "yuv420p", 640, 480)
+    with pytest.raises(VepError):
+        path.submit("nope", make_planes("yuv420p", 640, 480, 0))
+    path.close_stream("x")
+
+
+# ---- producer loop: gate + conversion + XADD against a fake Redis -----------------------------------
+class FakeRedis:
+    def __init__(self):
+        self.streams = {}
+
+    def xadd(self, name, fields, maxlen=None):
+        s = self.streams.setdefault(name, [])
+        s.append(bytes(fields["data"]))       # Redis copies the payload off the socket
+        if maxlen is not None:
+            del s[:-maxlen]
+
+
+class FakeFrame:
+    def __init__(self, planes, pts):
+        self.planes, self.pts, self.dts = planes, pts, pts - 1
+        self.width, self.height = planes[0].shape[1], planes[0].shape[0]
+        self.time_base = Fraction(1, 90000)
+        self.time = pts / 90000
+        self.pict_type = "I" if pts % 30 == 0 else "P"
+
+
+class FakePacket:
+    def __init__(self, idx, planes):
+        self.is_keyframe, self.is_corrupt, self.idx, self._planes = idx % 30 == 0, False, idx, planes
+        self.decoded = 0
+
+    def decode(self):
+        self.decoded += 1
+        return [FakeFrame(self._planes, self.idx)]
+
+
+def test_producer_keyframe_only_and_interval_skip(path):
+    r = FakeRedis()
+    now = [1_000_000]
+    prod = FrameProducer(path, r, now_ms=lambda: now[0])
+    w, h = 640, 480
+    prod.add_camera("kf", "yuv420p", w, h, memory_buffer=1)     # key-frame-only client
+    prod.add_camera("live", "yuv420p", w, h, memory_buffer=4)   # client polling every 10 packets
+    prod.add_camera("idle", "yuv420p", w, h)                    # nobody asked for >10 s
+    planes = {i: make_planes("yuv420p", w, h, i % 5) for i in range(60)}
+    pk = {c: [FakePacket(i, planes[i]) for i in range(60)] for c in ("kf", "live", "idle")}
+    for i in range(60):
+        now[0] += 40
+        ctl = {"kf": CameraControl(last_query=now[0] - 5, key_frame_only=True),
+               "live": CameraControl(last_query=now[0] - (i % 10) * 40 - 1),
+               "idle": CameraControl(last_query=now[0] - 60_000)}
+        for c in ("kf", "live", "idle"):
+            prod.on_packet(c, pk[c][i], ctl[c])
+        prod.flush()
+    VideoFrame, _ = W.dynamic_message_class()
+
+    def parse(b):
+        vf = VideoFrame()
+        vf.ParseFromString(b)
+        return vf
+
+    # key-frame-only: exactly the two keyframes were decoded; MAXLEN 1 keeps the newest
+    assert [p.idx for p in pk["kf"] if p.decoded] == [0, 30]
+    assert len(r.streams["kf"]) == 1
+    vf = parse(r.streams["kf"][0])
+    assert (vf.pts, vf.packet, vf.keyframe, vf.is_keyframe, vf.frame_type) == (30, 0, 2, True, "I")
+    assert np.array_equal(np.frombuffer(vf.data, np.uint8).reshape(h, w, 3), F.to_bgr24("yuv420p", planes[30]))
+    # live camera: every packet decoded exactly once (bursts catch up), ring keeps the newest 4
+    assert all(p.decoded == 1 for p in pk["live"])
+    assert [parse(b).pts for b in r.streams["live"]] == [56, 57, 58, 59]
+    last = parse(r.streams["live"][-1])
+    assert last.packet == 29 and last.keyframe == 2 and not last.is_keyframe
+    assert last.timestamp == int(59 / 90000 * 90000)
+    # idle camera: nothing decoded, nothing published
+    assert not any(p.decoded for p in pk["idle"]) and "idle" not in r.streams

@@ -1,0 +1,63 @@
+"""CPU: camera->GPU partition and the N>1 bench plumbing over gloo (world_size 2)."""
+import os
+import subprocess
+import sys
+
+from video_edge_ai_proxy_b200 import assign_cameras
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_block_assignment_64_cameras_8_gpus():
+    a = assign_cameras([(1920, 1080)] * 64, 8)
+    assert [len(r) for r in a] == [8] * 8
+    assert a[3] == list(range(24, 32))          # camera c -> GPU c // 8
+
+
+def test_balanced_assignment_mixed_fleet():
+    sizes = [(640, 480)] * 43 + [(1280, 720)] * 43 + [(1920, 1080)] * 42
+    a = assign_cameras(sizes, 8)
+    assert sorted(c for r in a for c in r) == list(range(128))
+    load = [sum(sizes[c][0] * sizes[c][1] for c in r) for r in a]
+    assert max(load) - min(load) <= 1920 * 1080
+    assert assign_cameras(sizes, 8) == a        # deterministic
+
+
+def test_uneven_and_degenerate():
+    assert assign_cameras([(2, 2)] * 3, 2) == [[0, 1], [2]]
+    assert assign_cameras([], 4) == [[], [], [], []]
+    assert assign_cameras([(2, 2)], 1) == [[0]]
+
+
+_WORKER = r'''
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+import bench
+dist.init_process_group("gloo", rank=int(os.environ["RANK"]), world_size=int(os.environ["WORLD_SIZE"]))
+rank, world = dist.get_rank(), dist.get_world_size()
+cams = bench.cameras_for_rank("16x1080p", rank, world)
+# every rank owns a disjoint, equal-sized camera set; no data-path collective
+gathered = [None] * world
+dist.all_gather_object(gathered, cams)
+ids = [c["camera"] for g in gathered for c in g]
+assert sorted(ids) == list(range(16 * world)), ids
+# timing reduction used by bench.py: max over ranks
+t = bench.max_over_ranks(1.0 + rank, device="cpu")
+assert t == float(world), t
+tot = bench.sum_over_ranks(len(cams), device="cpu")
+assert tot == 16 * world
+if rank == 0:
+    print("GLOO_OK")
+dist.destroy_process_group()
+'''
+
+
+def test_world_size_2_gloo_sharding(tmp_path):
+    script = tmp_path / "w.py"
+    script.write_text(_WORKER)
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29611", str(script), ROOT],
+                         capture_output=True, text=True, env=env, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "GLOO_OK" in out.stdout

@@ -1,0 +1,341 @@
+// vep_kernels.cuh — sm_100a kernels: batched YUV 4:2:0 -> BGR24 (planar limited/full range, NV12).
+//
+// Takes over the arithmetic of reference python/read_image.py:94 (`frame.to_ndarray('bgr24')`,
+// i.e. PyAV -> libswscale `sws_scale`).  Results are bit-exact with libswscale's default x86
+// path; the closed forms are restated in oracle/formulas.py (formulas A, B, C) and DESIGN.md.
+//
+// Shape of the work (HBM-bound byte arithmetic, no tensor cores): one launch covers every frame
+// of a tick.  A CTA looks up (frame, first item) in a per-CTA work table; each of its 8 warps
+// converts one "item" = 2 luma rows x 512 px.  A lane owns 16 px of both rows: two 16-byte Y
+// loads, one 8-byte U and one 8-byte V load (NV12: two 16-byte UV loads), so every chroma sample
+// is fetched once for its 2x2 luma block.  The 96 output bytes per lane are re-ordered through a
+// per-warp shared-memory tile so that global stores are 16 bytes per lane and contiguous across
+// the warp (3-byte pixels would otherwise scatter 48-byte strided pieces).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace vep {
+
+constexpr int kWarpsPerCta = 8;
+constexpr int kThreads = kWarpsPerCta * 32;
+constexpr int kSegPx = 512;                       // pixels per warp item row (32 lanes x 16 px)
+constexpr int kSegBytes = kSegPx * 3;             // 1536 output bytes per row of an item
+constexpr int kGenericBlocksPerCta = 1024;        // 2x2 blocks per CTA on the generic path
+
+enum : int { FMT_YUV420P = 0, FMT_YUVJ420P = 1, FMT_NV12 = 2 };
+
+struct __align__(16) FrameDev {   // 64 bytes, one per converted frame, lives in device memory
+    const uint8_t *y, *c0, *c1;   // Y, U|UV, V
+    uint8_t *dst;
+    int32_t sy, sc0, sc1, sd;     // strides in bytes
+    int32_t w, h;
+    int32_t fmt;
+    int32_t fast;                 // 1: width % 16 == 0 and all pointers/strides vector-aligned
+};
+struct CtaWork {                  // 8 bytes per CTA
+    int32_t frame;                // index into the FrameDev table
+    int32_t first;                // first warp item (fast path) / first 2x2 block (generic path)
+};
+
+// ---------------------------------------------------------------------------------------------
+// Fixed-point constants.  swscale x86 path (formula A):
+//   y  = (((Y<<3) - yOff) * yC) >> 16,   cb = (((u<<3)-1024) * ub) >> 16, ...
+// Each product is folded into one IMAD  t = sample * (8*coef) + add  whose UPPER 16 bits are the
+// floor-shifted term.  Biases ride in `add` so that halves can be combined as packed s16x2:
+//   y term carries -1024, cb/cr carry +1024, cgu/cgv carry +512 each (sum +1024).
+// ---------------------------------------------------------------------------------------------
+template <bool FULL> struct KA;
+template <> struct KA<false> { static constexpr int yC = 9539, vr = 13075, ub = 16525, ug = -3209, vg = -6660, yOff = 128; };
+template <> struct KA<true>  { static constexpr int yC = 8192, vr = 11485, ub = 14516, ug = -2819, vg = -5850, yOff = 0; };
+
+template <bool FULL> struct KM {
+    using K = KA<FULL>;
+    static constexpr int y_mul = 8 * K::yC,  y_add = -K::yOff * K::yC - (1024 << 16);
+    static constexpr int b_mul = 8 * K::ub,  b_add = -1024 * K::ub + (1024 << 16);
+    static constexpr int r_mul = 8 * K::vr,  r_add = -1024 * K::vr + (1024 << 16);
+    static constexpr int gu_mul = 8 * K::ug, gu_add = -1024 * K::ug + (512 << 16);
+    static constexpr int gv_mul = 8 * K::vg, gv_add = -1024 * K::vg + (512 << 16);
+};
+
+// swscale plain-C table path (formula B, limited range) — used by NV12's last two rows.
+struct KB {
+    static constexpr int cy = 76309, oy = 1048576, crv = 89830, cbu = 113537, cgu = -22049, cgv = -45756;
+    static constexpr int base = -(384 << 16) - oy + 326 * cy + 0x8000;
+    static constexpr int sub_r = crv >> 9, sub_b = cbu >> 9;
+    static constexpr int sub_gu = -((-cgu + 511) >> 9), sub_gv = -((-cgv + 511) >> 9);  // floor
+};
+
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) { return __byte_perm(a, b, sel); }
+__device__ __forceinline__ uint32_t byte_of(uint32_t w, int k) { return __byte_perm(w, 0, 0x4440 | k); }
+
+__device__ __forceinline__ uint4 ld_stream_v4(const uint8_t *p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ uint2 ld_stream_v2(const uint8_t *p) {
+    uint2 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ void st_stream_v4(uint8_t *p, const uint4 &v) {
+    asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// packed saturating add: per 16-bit lane max(min(a + b, 255), 0)  (VIADDMNMX.S16x2.RELU on sm_90+)
+__device__ __forceinline__ uint32_t add_sat_u8_x2(uint32_t a, uint32_t b) {
+    return __viaddmin_s16x2_relu(a, b, 0x00ff00ffu);
+}
+
+struct ChromaPair { uint32_t cb2, cg2, cr2; };   // each: the term (+bias) replicated in both s16 lanes
+
+// chroma terms from raw IMAD results (upper halves hold cb+1024, cr+1024, cgu+512, cgv+512)
+__device__ __forceinline__ ChromaPair chroma_pack(int tb, int tr, int tgu, int tgv) {
+    ChromaPair c;
+    c.cb2 = prmt((uint32_t)tb, (uint32_t)tb, 0x3232);
+    c.cr2 = prmt((uint32_t)tr, (uint32_t)tr, 0x3232);
+    const uint32_t tg = ((uint32_t)tgu & 0xffff0000u) + (uint32_t)tgv;   // upper half: cgu+cgv+1024, no carry in
+    c.cg2 = prmt(tg, tg, 0x3232);
+    return c;
+}
+template <bool FULL> __device__ __forceinline__ ChromaPair chroma_a(uint32_t u, uint32_t v) {
+    using M = KM<FULL>;   // u, v are plain samples (<<3 folded into the multiplier)
+    return chroma_pack((int)u * M::b_mul + M::b_add, (int)v * M::r_mul + M::r_add,
+                       (int)u * M::gu_mul + M::gu_add, (int)v * M::gv_mul + M::gv_add);
+}
+// NV12 even rows: su = u_up + u_cur, "(su<<2) - 1024" -> half the multiplier
+__device__ __forceinline__ ChromaPair chroma_a_sum2(uint32_t su, uint32_t sv) {
+    using M = KM<false>;
+    return chroma_pack((int)su * (M::b_mul / 2) + M::b_add, (int)sv * (M::r_mul / 2) + M::r_add,
+                       (int)su * (M::gu_mul / 2) + M::gu_add, (int)sv * (M::gv_mul / 2) + M::gv_add);
+}
+
+// 4 luma samples (one 32-bit word) + the two chroma pairs covering them -> 12 output bytes
+template <bool FULL>
+__device__ __forceinline__ void luma4_a(uint32_t yw, const ChromaPair &P, const ChromaPair &Q,
+                                        uint32_t &w0, uint32_t &w1, uint32_t &w2) {
+    using M = KM<FULL>;
+    const int t0 = (int)byte_of(yw, 0) * M::y_mul + M::y_add;
+    const int t1 = (int)byte_of(yw, 1) * M::y_mul + M::y_add;
+    const int t2 = (int)byte_of(yw, 2) * M::y_mul + M::y_add;
+    const int t3 = (int)(yw >> 24) * M::y_mul + M::y_add;
+    const uint32_t yp = prmt((uint32_t)t0, (uint32_t)t1, 0x7632);   // [y0-1024, y1-1024] as s16x2
+    const uint32_t yq = prmt((uint32_t)t2, (uint32_t)t3, 0x7632);
+    const uint32_t bp = add_sat_u8_x2(yp, P.cb2), gp = add_sat_u8_x2(yp, P.cg2), rp = add_sat_u8_x2(yp, P.cr2);
+    const uint32_t bq = add_sat_u8_x2(yq, Q.cb2), gq = add_sat_u8_x2(yq, Q.cg2), rq = add_sat_u8_x2(yq, Q.cr2);
+    const uint32_t bgp = gp * 256u + bp;   // [B0 G0 B1 G1]
+    const uint32_t bgq = gq * 256u + bq;   // [B2 G2 B3 G3]
+    w0 = prmt(bgp, rp, 0x2410);            // B0 G0 R0 B1
+    const uint32_t x = prmt(bgp, rp, 0x0063);   // G1 R1 . .
+    w1 = prmt(x, bgq, 0x5410);             // G1 R1 B2 G2
+    w2 = prmt(bgq, rq, 0x6324);            // R2 B3 G3 R3
+}
+
+// formula B on one 32-bit word of luma; kb/kg/kr = base + d*cy for the two chroma columns
+struct ChromaB { int kb, kg, kr; };
+__device__ __forceinline__ ChromaB chroma_b(int u, int v) {
+    ChromaB c;
+    const int db = ((u * KB::cbu) >> 16) - KB::sub_b;
+    const int dr = ((v * KB::crv) >> 16) - KB::sub_r;
+    const int dg = ((u * KB::cgu) >> 16) - KB::sub_gu + ((v * KB::cgv) >> 16) - KB::sub_gv;
+    c.kb = KB::base + db * KB::cy;
+    c.kg = KB::base + dg * KB::cy;
+    c.kr = KB::base + dr * KB::cy;
+    return c;
+}
+__device__ __forceinline__ uint32_t clamp_pair_hi(int a, int b) {   // [sat_u8(a>>16), sat_u8(b>>16)] as s16x2
+    return __vimin_s16x2_relu(prmt((uint32_t)a, (uint32_t)b, 0x7632), 0x00ff00ffu);
+}
+__device__ __forceinline__ void luma4_b(uint32_t yw, const ChromaB &P, const ChromaB &Q,
+                                        uint32_t &w0, uint32_t &w1, uint32_t &w2) {
+    const int y0 = (int)byte_of(yw, 0) * KB::cy, y1 = (int)byte_of(yw, 1) * KB::cy;
+    const int y2 = (int)byte_of(yw, 2) * KB::cy, y3 = (int)(yw >> 24) * KB::cy;
+    const uint32_t bp = clamp_pair_hi(y0 + P.kb, y1 + P.kb), gp = clamp_pair_hi(y0 + P.kg, y1 + P.kg),
+                   rp = clamp_pair_hi(y0 + P.kr, y1 + P.kr);
+    const uint32_t bq = clamp_pair_hi(y2 + Q.kb, y3 + Q.kb), gq = clamp_pair_hi(y2 + Q.kg, y3 + Q.kg),
+                   rq = clamp_pair_hi(y2 + Q.kr, y3 + Q.kr);
+    const uint32_t bgp = gp * 256u + bp, bgq = gq * 256u + bq;
+    w0 = prmt(bgp, rp, 0x2410);
+    const uint32_t x = prmt(bgp, rp, 0x0063);
+    w1 = prmt(x, bgq, 0x5410);
+    w2 = prmt(bgq, rq, 0x6324);
+}
+
+__device__ __forceinline__ uint32_t word_of(const uint4 &v, int i) { return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w; }
+
+// ---- one lane's 16 px x 2 rows, planar ------------------------------------------------------
+template <bool FULL>
+__device__ __forceinline__ void lane_planar(const FrameDev &f, int rp, int x, uint32_t (&o0)[12], uint32_t (&o1)[12]) {
+    const uint4 ya = ld_stream_v4(f.y + (size_t)(2 * rp) * f.sy + x);
+    const uint4 yb = ld_stream_v4(f.y + (size_t)(2 * rp + 1) * f.sy + x);
+    const uint2 uu = ld_stream_v2(f.c0 + (size_t)rp * f.sc0 + (x >> 1));
+    const uint2 vv = ld_stream_v2(f.c1 + (size_t)rp * f.sc1 + (x >> 1));
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        const uint32_t uw = g < 2 ? uu.x : uu.y, vw = g < 2 ? vv.x : vv.y;
+        const int b = (g & 1) * 2;
+        const ChromaPair P = chroma_a<FULL>(byte_of(uw, b), byte_of(vw, b));
+        const ChromaPair Q = chroma_a<FULL>(b == 2 ? (uw >> 24) : byte_of(uw, 1), b == 2 ? (vw >> 24) : byte_of(vw, 1));
+        luma4_a<FULL>(word_of(ya, g), P, Q, o0[3 * g], o0[3 * g + 1], o0[3 * g + 2]);
+        luma4_a<FULL>(word_of(yb, g), P, Q, o1[3 * g], o1[3 * g + 1], o1[3 * g + 2]);
+    }
+}
+
+// ---- one lane's 16 px x 2 rows, NV12 (formula C) -----------------------------------------------
+__device__ __forceinline__ void lane_nv12(const FrameDev &f, int rp, int x, uint32_t (&o0)[12], uint32_t (&o1)[12]) {
+    const uint4 ya = ld_stream_v4(f.y + (size_t)(2 * rp) * f.sy + x);
+    const uint4 yb = ld_stream_v4(f.y + (size_t)(2 * rp + 1) * f.sy + x);
+    const int up = rp > 0 ? rp - 1 : 0;
+    const uint4 cu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)rp * f.sc0 + x));   // u0 v0 u1 v1 ...
+    const uint4 pu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)up * f.sc0 + x));   // row above (L2/L1 hit)
+    const bool tail = (rp == (f.h >> 1) - 1);   // rows H-2, H-1: swscale leaves its SIMD output stage
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        const uint32_t c = word_of(cu, g), p = word_of(pu, g);
+        const uint32_t u0 = byte_of(c, 0), v0 = byte_of(c, 1), u1 = byte_of(c, 2), v1 = c >> 24;
+        const uint32_t pu0 = byte_of(p, 0), pv0 = byte_of(p, 1), pu1 = byte_of(p, 2), pv1 = p >> 24;
+        if (!tail) {
+            const ChromaPair Pe = chroma_a_sum2(pu0 + u0, pv0 + v0), Qe = chroma_a_sum2(pu1 + u1, pv1 + v1);
+            const ChromaPair Po = chroma_a<false>(u0, v0), Qo = chroma_a<false>(u1, v1);
+            luma4_a<false>(word_of(ya, g), Pe, Qe, o0[3 * g], o0[3 * g + 1], o0[3 * g + 2]);
+            luma4_a<false>(word_of(yb, g), Po, Qo, o1[3 * g], o1[3 * g + 1], o1[3 * g + 2]);
+        } else {
+            // row H-2: 12-bit blend 1/4 above + 3/4 current (rounded); row H-1: current row as is
+            const ChromaB Pe = chroma_b((int)(pu0 * 1024u + u0 * 3072u + 2048u) >> 12, (int)(pv0 * 1024u + v0 * 3072u + 2048u) >> 12);
+            const ChromaB Qe = chroma_b((int)(pu1 * 1024u + u1 * 3072u + 2048u) >> 12, (int)(pv1 * 1024u + v1 * 3072u + 2048u) >> 12);
+            const ChromaB Po = chroma_b((int)u0, (int)v0), Qo = chroma_b((int)u1, (int)v1);
+            luma4_b(word_of(ya, g), Pe, Qe, o0[3 * g], o0[3 * g + 1], o0[3 * g + 2]);
+            luma4_b(word_of(yb, g), Po, Qo, o1[3 * g], o1[3 * g + 1], o1[3 * g + 2]);
+        }
+    }
+}
+
+// ---- generic path: one 2x2 block per step, scalar, any even geometry / alignment ----------------
+__device__ __forceinline__ uint8_t sat8(int v) { return (uint8_t)min(max(v, 0), 255); }
+
+template <bool FULL>
+__device__ __forceinline__ void px_a(int Y, int Uw, int Vw, uint8_t *d) {
+    using K = KA<FULL>;
+    const int y = (((Y << 3) - K::yOff) * K::yC) >> 16;
+    const int cb = (Uw * K::ub) >> 16, cr = (Vw * K::vr) >> 16;
+    const int cg = ((Uw * K::ug) >> 16) + ((Vw * K::vg) >> 16);
+    d[0] = sat8(y + cb); d[1] = sat8(y + cg); d[2] = sat8(y + cr);
+}
+__device__ __forceinline__ void px_b(int Y, int u, int v, uint8_t *d) {
+    const ChromaB c = chroma_b(u, v);
+    d[0] = sat8((Y * KB::cy + c.kb) >> 16); d[1] = sat8((Y * KB::cy + c.kg) >> 16); d[2] = sat8((Y * KB::cy + c.kr) >> 16);
+}
+
+__device__ __forceinline__ void generic_block(const FrameDev &f, int bx, int by) {
+    const uint8_t *y0 = f.y + (size_t)(2 * by) * f.sy + 2 * bx, *y1 = y0 + f.sy;
+    uint8_t *d0 = f.dst + (size_t)(2 * by) * f.sd + 6 * bx, *d1 = d0 + f.sd;
+    if (f.fmt != FMT_NV12) {
+        const int Uw = ((int)f.c0[(size_t)by * f.sc0 + bx] << 3) - 1024;
+        const int Vw = ((int)f.c1[(size_t)by * f.sc1 + bx] << 3) - 1024;
+        if (f.fmt == FMT_YUVJ420P) {
+            px_a<true>(y0[0], Uw, Vw, d0); px_a<true>(y0[1], Uw, Vw, d0 + 3);
+            px_a<true>(y1[0], Uw, Vw, d1); px_a<true>(y1[1], Uw, Vw, d1 + 3);
+        } else {
+            px_a<false>(y0[0], Uw, Vw, d0); px_a<false>(y0[1], Uw, Vw, d0 + 3);
+            px_a<false>(y1[0], Uw, Vw, d1); px_a<false>(y1[1], Uw, Vw, d1 + 3);
+        }
+        return;
+    }
+    const int up = by > 0 ? by - 1 : 0;
+    const uint8_t *c = f.c0 + (size_t)by * f.sc0 + 2 * bx, *p = f.c0 + (size_t)up * f.sc0 + 2 * bx;
+    const int u = c[0], v = c[1], pu = p[0], pv = p[1];
+    if (by != (f.h >> 1) - 1) {
+        const int Ue = ((pu + u) << 2) - 1024, Ve = ((pv + v) << 2) - 1024;
+        const int Uo = (u << 3) - 1024, Vo = (v << 3) - 1024;
+        px_a<false>(y0[0], Ue, Ve, d0); px_a<false>(y0[1], Ue, Ve, d0 + 3);
+        px_a<false>(y1[0], Uo, Vo, d1); px_a<false>(y1[1], Uo, Vo, d1 + 3);
+    } else {
+        const int ue = (pu * 1024 + u * 3072 + 2048) >> 12, ve = (pv * 1024 + v * 3072 + 2048) >> 12;
+        px_b(y0[0], ue, ve, d0); px_b(y0[1], ue, ve, d0 + 3);
+        px_b(y1[0], u, v, d1);   px_b(y1[1], u, v, d1 + 3);
+    }
+}
+
+// ---- the batched kernel -------------------------------------------------------------------------
+// STORE_MODE 0: shared-memory re-order, then 16 B/lane warp-contiguous st.global
+//            1: shared-memory tile written out by the TMA unit (cp.async.bulk shared -> global)
+//            2: direct 16 B stores from registers (48 B stride between lanes; for comparison)
+template <int STORE_MODE>
+__global__ void __launch_bounds__(kThreads)
+yuv_to_bgr24_batched(const FrameDev *__restrict__ frames, const CtaWork *__restrict__ work) {
+    __shared__ __align__(128) uint8_t tile[kWarpsPerCta][2][kSegBytes];
+    const CtaWork cw = work[blockIdx.x];
+    const FrameDev f = frames[cw.frame];
+
+    if (!f.fast) {
+        const int bw = f.w >> 1, nblk = bw * (f.h >> 1);
+        for (int q = cw.first + threadIdx.x; q < min(cw.first + kGenericBlocksPerCta, nblk); q += kThreads)
+            generic_block(f, q % bw, q / bw);
+        return;
+    }
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int segs = (f.w + kSegPx - 1) / kSegPx;
+    const int item = cw.first + warp;
+    if (item >= segs * (f.h >> 1)) return;   // warp-uniform
+    const int rp = item / segs, seg = item - rp * segs;
+    const int x = seg * kSegPx + lane * 16;
+
+    uint32_t o0[12], o1[12];
+    const bool active = x < f.w;
+    if (active) {
+        if (f.fmt == FMT_YUV420P) lane_planar<false>(f, rp, x, o0, o1);
+        else if (f.fmt == FMT_YUVJ420P) lane_planar<true>(f, rp, x, o0, o1);
+        else lane_nv12(f, rp, x, o0, o1);
+    }
+    uint8_t *g0 = f.dst + (size_t)(2 * rp) * f.sd + (size_t)seg * kSegBytes;
+    uint8_t *g1 = g0 + f.sd;
+    const int seg_bytes = min(kSegPx, f.w - seg * kSegPx) * 3;   // multiple of 48
+
+    if (STORE_MODE == 2) {
+        if (active) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                st_stream_v4(g0 + lane * 48 + k * 16, make_uint4(o0[4 * k], o0[4 * k + 1], o0[4 * k + 2], o0[4 * k + 3]));
+                st_stream_v4(g1 + lane * 48 + k * 16, make_uint4(o1[4 * k], o1[4 * k + 1], o1[4 * k + 2], o1[4 * k + 3]));
+            }
+        }
+        return;
+    }
+
+    uint8_t *t0 = tile[warp][0], *t1 = tile[warp][1];
+    if (active) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {   // 48 B lane stride: conflict-free per quarter warp
+            *reinterpret_cast<uint4 *>(t0 + lane * 48 + k * 16) = make_uint4(o0[4 * k], o0[4 * k + 1], o0[4 * k + 2], o0[4 * k + 3]);
+            *reinterpret_cast<uint4 *>(t1 + lane * 48 + k * 16) = make_uint4(o1[4 * k], o1[4 * k + 1], o1[4 * k + 2], o1[4 * k + 3]);
+        }
+    }
+    if (STORE_MODE == 0) {
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const int off = (k * 32 + lane) * 16;
+            if (off < seg_bytes) {
+                st_stream_v4(g0 + off, *reinterpret_cast<const uint4 *>(t0 + off));
+                st_stream_v4(g1 + off, *reinterpret_cast<const uint4 *>(t1 + off));
+            }
+        }
+    } else {
+        // make the generic-proxy smem writes visible to the async proxy, then one lane hands both
+        // rows to the TMA unit (UBLKCP shared -> global); smem must outlive the read.
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) {
+            const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(t0), s1 = (uint32_t)__cvta_generic_to_shared(t1);
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(g0), "r"(s0), "r"(seg_bytes) : "memory");
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(g1), "r"(s1), "r"(seg_bytes) : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        }
+    }
+}
+
+}  // namespace vep
