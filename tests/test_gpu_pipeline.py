@@ -133,10 +133,28 @@ def test_two_ticks_in_flight_and_zero_copy_staging(path):
             got.append(path.result("cam").copy())
     path.tick_wait()
     got.append(path.result("cam").copy())
-    with pytest.raises(VepError):
-        path.tick_begin(); path.tick_begin(); path.tick_begin()
     for g, pl in zip(got, frames):
         assert np.array_equal(g, F.to_bgr24("nv12", pl))
+
+
+def test_at_most_two_ticks_in_flight(path):
+    w, h = 64, 16
+    path.open_stream("cam", "yuv420p", w, h)
+    for s in range(2):
+        path.submit("cam", make_planes("yuv420p", w, h, s))
+        assert path.tick_begin() == 1
+    path.submit("cam", make_planes("yuv420p", w, h, 2))
+    with pytest.raises(VepError) as e:
+        path.tick_begin()
+    assert e.value.status == _abi.VEP_ERR_BUSY
+    with pytest.raises(VepError) as e:
+        path.close_stream("cam")          # refused while ticks are in flight
+    assert e.value.status == _abi.VEP_ERR_BUSY
+    path.tick_wait(); path.tick_wait()
+    assert path.tick() == 1
+    assert np.array_equal(path.result("cam"), F.to_bgr24("yuv420p", make_planes("yuv420p", w, h, 2)))
+    assert path.tick_begin() == 0         # an empty tick is not counted as in flight
+    path.tick_wait()
 
 
 def test_concurrent_producers_one_thread_per_camera(path):
@@ -231,7 +249,7 @@ def test_producer_keyframe_only_and_interval_skip(path):
     for i in range(60):
         now[0] += 40
         ctl = {"kf": CameraControl(last_query=now[0] - 5, key_frame_only=True),
-               "live": CameraControl(last_query=now[0] - (i % 10) * 40 - 1),
+               "live": CameraControl(last_query=now[0] - ((i + 1) % 10) * 40 - 1),   # fresh query at i = 9, 19, ...
                "idle": CameraControl(last_query=now[0] - 60_000)}
         for c in ("kf", "live", "idle"):
             prod.on_packet(c, pk[c][i], ctl[c])

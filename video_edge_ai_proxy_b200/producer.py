@@ -17,6 +17,7 @@ from __future__ import annotations
 import time
 from typing import Dict, List, Optional
 
+from ._abi import VEP_ERR_BUSY, VepError
 from .frame_path import FramePath, make_meta
 from .gate import CameraControl, DecodeGate, camera_active
 
@@ -68,7 +69,13 @@ class FrameProducer:
                                  keyframe=o.keyframe, time_base=float(frame.time_base),
                                  is_keyframe=o.is_keyframe, is_corrupt=o.is_corrupt,
                                  frame_type=frame.pict_type)
-                self.path.submit(device_id, frame.planes, meta)
+                try:
+                    self.path.submit(device_id, frame.planes, meta)
+                except VepError as e:
+                    if e.status != VEP_ERR_BUSY:
+                        raise
+                    self.flush()      # a long catch-up burst filled this camera's staging ring:
+                    self.path.submit(device_id, frame.planes, meta)   # convert + publish, then go on
                 cam.staged += 1
                 staged += 1
                 if o.first_frame_only:
