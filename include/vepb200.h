@@ -22,6 +22,7 @@ extern "C" {
 #endif
 
 #define VEP_ABI_VERSION 1
+#define VEP_MAX_TICKS_IN_FLIGHT 4
 
 typedef enum {
     VEP_OK = 0,
@@ -113,8 +114,8 @@ int vep_commit_input(vep_ctx *ctx, int stream_id, const vep_frame_meta *meta);
 
 /* One tick: for every stream with a committed frame — H2D on that camera's CUDA stream, ONE
  * batched kernel launch over all of them, D2H into the pinned output ring.  vep_tick is
- * begin+wait.  At most 2 ticks may be in flight (begin, begin, wait, …) so H2D of tick t+1
- * overlaps D2H of tick t. */
+ * begin+wait.  Up to VEP_MAX_TICKS_IN_FLIGHT ticks may be in flight (begin, begin, wait, …) so the
+ * staging copy and H2D of later ticks overlap the D2H of earlier ones (PCIe is full duplex). */
 int vep_tick_begin(vep_ctx *ctx, int *n_frames);
 int vep_tick_wait(vep_ctx *ctx);
 int vep_tick(vep_ctx *ctx, int *n_frames);

@@ -175,6 +175,42 @@ def test_linearity_free_properties_at_full_size(path):
     plan.close()
 
 
+def test_persistent_tma_kernel_bit_identical(golden_pixels, small_frames):
+    """The alternative kernel (VEP_KERNEL=persistent: per-warp TMA bulk-copy pipelines) on every path."""
+    old = os.environ.get("VEP_KERNEL")
+    os.environ["VEP_KERNEL"] = "persistent"
+    try:
+        with FramePath(0) as p:
+            for r in golden_pixels["rows"]:
+                if r["path"] == "simd":
+                    out = gpu_convert(p, r["fmt"], make_planes(r["fmt"], r["w"], r["h"], r["seed"]))
+                    assert _digest(out) == (r["sum"], r["sha256"]), r
+            for fmt, w, h, seed, planes, want in small_frames:
+                assert np.array_equal(gpu_convert(p, fmt, planes), want), (fmt, w, h)
+            for fmt, w, h in (("yuv420p", 16, 8), ("yuv420p", 48, 8), ("nv12", 528, 16), ("yuvj420p", 1040, 8), ("nv12", 32, 8),
+                              ("yuv420p", 64, 8), ("yuv420p", 496, 4), ("nv12", 18, 10)):
+                planes = make_planes(fmt, w, h, w + h)
+                assert np.array_equal(gpu_convert(p, fmt, planes), F.to_bgr24(fmt, planes)), (fmt, w, h)
+            # a mixed batch in one launch: bulk, vector and generic frames together
+            specs = [("yuv420p", 1920, 1080, 1), ("nv12", 1280, 720, 2), ("yuv420p", 48, 8, 3), ("yuvj420p", 642, 482, 4), ("nv12", 3840, 2160, 5)]
+            descs, keep = [], []
+            for fmt, w, h, seed in specs:
+                planes = make_planes(fmt, w, h, seed)
+                t = [torch.from_numpy(q).cuda() for q in planes]
+                out = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+                descs.append(desc_from_tensors(fmt, t, out))
+                keep.append((fmt, planes, t, out))
+            p.convert_batch(descs, torch.cuda.current_stream().cuda_stream)
+            torch.cuda.synchronize()
+            for fmt, planes, t, out in keep:
+                assert np.array_equal(out.cpu().numpy(), F.to_bgr24(fmt, planes)), fmt
+    finally:
+        if old is None:
+            os.environ.pop("VEP_KERNEL", None)
+        else:
+            os.environ["VEP_KERNEL"] = old
+
+
 def test_all_store_modes_bit_identical():
     planes = make_planes("yuv420p", 1920, 1080, 42)
     want = F.to_bgr24("yuv420p", planes)

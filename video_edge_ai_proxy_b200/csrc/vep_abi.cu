@@ -8,6 +8,8 @@
 #include "vep_kernels.cuh"
 #include "../../include/vepb200.h"
 
+#include <immintrin.h>
+
 #include <algorithm>
 #include <cstdarg>
 #include <cstddef>
@@ -22,7 +24,8 @@
 static_assert(sizeof(vep_frame_desc) == 72 && offsetof(vep_frame_desc, dst) == 40 && offsetof(vep_frame_desc, width) == 52,
               "vep_frame_desc layout is part of the ABI (mirrored in _abi.py)");
 static_assert(sizeof(vep_frame_meta) == 64 && offsetof(vep_frame_meta, frame_type) == 56, "vep_frame_meta layout is part of the ABI");
-static_assert(sizeof(vep::FrameDev) == 64 && sizeof(vep::CtaWork) == 8, "device table layout");
+static_assert(sizeof(vep::FrameDev) == 80 && offsetof(vep::FrameDev, w) == 48 && offsetof(vep::FrameDev, item_begin) == 64 &&
+              sizeof(vep::CtaWork) == 8, "device table layout (the kernels read 16-byte groups of FrameDev)");
 
 using vep::CtaWork;
 using vep::FrameDev;
@@ -68,10 +71,11 @@ extern "C" const char *vep_status_name(int s) {
 static constexpr int kMaxDim = 16384;
 
 struct Tables {
-    std::vector<FrameDev> frames;
-    std::vector<CtaWork> work;
+    std::vector<FrameDev> frames;   // n_converted entries + 1 sentinel (item_begin = total_items)
+    std::vector<CtaWork> work;      // per-CTA table of the one-shot kernel
     int64_t alg_bytes = 0;
     int n_converted = 0;
+    int total_items = 0;            // item space of the persistent kernel
 };
 
 static inline bool aligned(const void *p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
@@ -82,6 +86,7 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t) {
     t.work.clear();
     t.alg_bytes = 0;
     t.n_converted = 0;
+    t.total_items = 0;
     for (int i = 0; i < n; ++i) {
         const vep_frame_desc &s = d[i];
         if (!s.convert) continue;
@@ -95,25 +100,37 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t) {
         const int cw = nv12 ? w : w / 2;
         if (s.stride[0] < w || s.stride[1] < cw || (!nv12 && s.stride[2] < cw) || s.dst_stride < 3 * w)
             return fail(VEP_ERR_GEOMETRY, "desc %d: a stride is smaller than its row", i);
-        FrameDev f;
+        FrameDev f{};
         f.y = s.plane[0]; f.c0 = s.plane[1]; f.c1 = nv12 ? nullptr : s.plane[2]; f.dst = s.dst;
         f.sy = s.stride[0]; f.sc0 = s.stride[1]; f.sc1 = nv12 ? 0 : s.stride[2]; f.sd = s.dst_stride;
         f.w = w; f.h = h; f.fmt = s.fmt;
         const size_t ca = nv12 ? 16 : 8;
-        f.fast = (w % 16 == 0) && aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
-                 (nv12 || (aligned(f.c1, 8) && f.sc1 % 8 == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
+        const bool vec = (w % 16 == 0) && aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
+                         (nv12 || (aligned(f.c1, 8) && f.sc1 % 8 == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
+        const bool bulk = vec && (w % 32 == 0) && aligned(f.c0, 16) && f.sc0 % 16 == 0 && (nv12 || (aligned(f.c1, 16) && f.sc1 % 16 == 0));
+        f.fast = bulk ? vep::PATH_BULK : vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;
+        f.segs = (w + vep::kSegPx - 1) / vep::kSegPx;
+        f.segs_magic = f.segs == 1 ? 0u : (uint32_t)((((uint64_t)1 << 32) + f.segs - 1) / f.segs);
+        f.item_begin = t.total_items;
         const int fi = (int)t.frames.size();
         t.frames.push_back(f);
-        if (f.fast) {
-            const int items = ((w + vep::kSegPx - 1) / vep::kSegPx) * (h / 2);
+        int items;
+        if (f.fast != vep::PATH_GENERIC) {
+            items = f.segs * (h / 2);
             for (int it = 0; it < items; it += vep::kWarpsPerCta) t.work.push_back(CtaWork{fi, it});
         } else {
             const int blocks = (w / 2) * (h / 2);
+            items = (blocks + vep::kGenericBlocksPerCta - 1) / vep::kGenericBlocksPerCta;
             for (int b = 0; b < blocks; b += vep::kGenericBlocksPerCta) t.work.push_back(CtaWork{fi, b});
         }
+        if ((int64_t)t.total_items + items > (int64_t)1 << 30) return fail(VEP_ERR_INVALID_ARG, "batch too large");
+        t.total_items += items;
         t.alg_bytes += (int64_t)w * h * 9 / 2;
         t.n_converted++;
     }
+    FrameDev sentinel{};
+    sentinel.item_begin = t.total_items;
+    t.frames.push_back(sentinel);
     return VEP_OK;
 }
 
@@ -164,13 +181,15 @@ struct TickRec {
 
 struct vep_ctx {
     int device = 0;
-    int store_mode = 0;
+    int kernel = 1;              // 1: one-shot CTA-per-tile (default), 0: persistent TMA-pipelined (VEP_KERNEL=persistent)
+    int store_mode = 0;          // one-shot kernel only (VEP_STORE_MODE)
+    int resident_warps = 0;      // persistent kernel: warps the whole GPU keeps resident
     cudaStream_t main = nullptr;
     TableBuf tb[4];
     int tb_next = 0;
     std::mutex mu;                                  // guards streams map, ticks, table buffers
     std::unordered_map<int, Stream *> streams;
-    TickRec ticks[2];
+    TickRec ticks[VEP_MAX_TICKS_IN_FLIGHT];
     int tick_head = 0, ticks_in_flight = 0;         // oldest in flight = tick_head
     vep_stats stats{};
     Tables scratch;
@@ -180,7 +199,7 @@ struct vep_plan {
     vep_ctx *ctx = nullptr;
     FrameDev *d_frames = nullptr;
     CtaWork *d_work = nullptr;
-    int n_ctas = 0, n_converted = 0;
+    int n_ctas = 0, n_converted = 0, total_items = 0;
     int64_t alg_bytes = 0;
 };
 
@@ -190,12 +209,23 @@ struct DeviceGuard {
     ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 
-static int launch_tables(int store_mode, const FrameDev *d_frames, const CtaWork *d_work, int n_ctas, cudaStream_t st) {
-    if (n_ctas <= 0) return VEP_OK;
-    switch (store_mode) {
-        case 1: vep::yuv_to_bgr24_batched<1><<<n_ctas, vep::kThreads, 0, st>>>(d_frames, d_work); break;
-        case 2: vep::yuv_to_bgr24_batched<2><<<n_ctas, vep::kThreads, 0, st>>>(d_frames, d_work); break;
-        default: vep::yuv_to_bgr24_batched<0><<<n_ctas, vep::kThreads, 0, st>>>(d_frames, d_work); break;
+// grid of the persistent kernel: every warp gets the same number of items (no partial last round)
+static int persistent_ctas(const vep_ctx *c, int total_items) {
+    const int rounds = (total_items + c->resident_warps - 1) / c->resident_warps;
+    const int warps = (total_items + rounds - 1) / rounds;
+    return (warps + vep::kPWarps - 1) / vep::kPWarps;
+}
+
+static int launch_tables(const vep_ctx *c, const FrameDev *d_frames, const CtaWork *d_work, int n_ctas, int total_items, cudaStream_t st) {
+    if (total_items <= 0) return VEP_OK;
+    if (c->kernel == 0) {
+        vep::yuv_to_bgr24_persistent<<<persistent_ctas(c, total_items), vep::kPThreads, vep::kPSmemBytes, st>>>(d_frames, total_items);
+    } else {
+        switch (c->store_mode) {
+            case 1: vep::yuv_to_bgr24_batched<1><<<n_ctas, vep::kThreads, 0, st>>>(d_frames, d_work); break;
+            case 2: vep::yuv_to_bgr24_batched<2><<<n_ctas, vep::kThreads, 0, st>>>(d_frames, d_work); break;
+            default: vep::yuv_to_bgr24_batched<0><<<n_ctas, vep::kThreads, 0, st>>>(d_frames, d_work); break;
+        }
     }
     CUDA_TRY(cudaGetLastError());
     return VEP_OK;
@@ -219,6 +249,16 @@ extern "C" int vep_create(int device, vep_ctx **out) {
     const char *sm = getenv("VEP_STORE_MODE");
     c->store_mode = sm ? atoi(sm) : 0;
     if (c->store_mode < 0 || c->store_mode > 2) c->store_mode = 0;
+    const char *kn = getenv("VEP_KERNEL");
+    c->kernel = (kn && strcmp(kn, "persistent") == 0) ? 0 : 1;   // default: one-shot (the faster one)
+    CUDA_TRY(cudaFuncSetAttribute(vep::yuv_to_bgr24_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, vep::kPSmemBytes));
+    CUDA_TRY(cudaFuncSetAttribute(vep::yuv_to_bgr24_persistent, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    int per_sm = 0;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vep::yuv_to_bgr24_persistent, vep::kPThreads, vep::kPSmemBytes));
+    if (per_sm < 1) return fail(VEP_ERR_CUDA, "persistent kernel does not fit on an SM");
+    const char *occ = getenv("VEP_CTAS_PER_SM");
+    if (occ && atoi(occ) >= 1 && atoi(occ) < per_sm) per_sm = atoi(occ);
+    c->resident_warps = per_sm * prop.multiProcessorCount * vep::kPWarps;
     CUDA_TRY(cudaStreamCreateWithFlags(&c->main, cudaStreamNonBlocking));
     for (auto &t : c->tb) CUDA_TRY(cudaEventCreateWithFlags(&t.used, cudaEventDisableTiming));
     for (auto &t : c->ticks) { CUDA_TRY(cudaEventCreate(&t.k0)); CUDA_TRY(cudaEventCreate(&t.k1)); }
@@ -250,7 +290,7 @@ extern "C" void vep_destroy(vep_ctx *c) {
 
 // upload `t` through the next ring buffer and launch on `st`
 static int upload_and_launch(vep_ctx *c, const Tables &t, cudaStream_t st) {
-    if (t.work.empty()) return VEP_OK;
+    if (t.total_items == 0) return VEP_OK;
     TableBuf &b = c->tb[c->tb_next];
     c->tb_next = (c->tb_next + 1) % 4;
     if (b.pending) { CUDA_TRY(cudaEventSynchronize(b.used)); b.pending = false; }
@@ -269,7 +309,7 @@ static int upload_and_launch(vep_ctx *c, const Tables &t, cudaStream_t st) {
     memcpy(b.h, t.frames.data(), t.frames.size() * sizeof(FrameDev));
     memcpy((char *)b.h + fb, t.work.data(), t.work.size() * sizeof(CtaWork));
     CUDA_TRY(cudaMemcpyAsync(b.d, b.h, need, cudaMemcpyHostToDevice, st));
-    int rc = launch_tables(c->store_mode, (const FrameDev *)b.d, (const CtaWork *)((char *)b.d + fb), (int)t.work.size(), st);
+    int rc = launch_tables(c, (const FrameDev *)b.d, (const CtaWork *)((char *)b.d + fb), (int)t.work.size(), t.total_items, st);
     if (rc) return rc;
     CUDA_TRY(cudaEventRecord(b.used, st));
     b.pending = true;
@@ -299,10 +339,11 @@ extern "C" int vep_plan_create(vep_ctx *c, const vep_frame_desc *descs, int n, v
     vep_plan *p = new (std::nothrow) vep_plan();
     if (!p) return fail(VEP_ERR_NOMEM, "out of host memory");
     p->ctx = c;
-    p->n_ctas = (int)t.work.size();
+    p->n_ctas = c->kernel == 0 ? (t.total_items ? persistent_ctas(c, t.total_items) : 0) : (int)t.work.size();
+    p->total_items = t.total_items;
     p->n_converted = t.n_converted;
     p->alg_bytes = t.alg_bytes;
-    if (p->n_ctas) {
+    if (t.total_items) {
         cudaError_t e = cudaMalloc(&p->d_frames, t.frames.size() * sizeof(FrameDev));
         if (e == cudaSuccess) e = cudaMalloc(&p->d_work, t.work.size() * sizeof(CtaWork));
         if (e == cudaSuccess) e = cudaMemcpy(p->d_frames, t.frames.data(), t.frames.size() * sizeof(FrameDev), cudaMemcpyHostToDevice);
@@ -321,7 +362,7 @@ extern "C" int vep_plan_create(vep_ctx *c, const vep_frame_desc *descs, int n, v
 extern "C" int vep_plan_launch(vep_plan *p, void *cuda_stream) {
     if (!p) return fail(VEP_ERR_INVALID_ARG, "plan is null");
     DeviceGuard g(p->ctx->device);
-    int rc = launch_tables(p->ctx->store_mode, p->d_frames, p->d_work, p->n_ctas, (cudaStream_t)cuda_stream);
+    int rc = launch_tables(p->ctx, p->d_frames, p->d_work, p->n_ctas, p->total_items, (cudaStream_t)cuda_stream);
     if (rc) return rc;
     p->ctx->stats.kernel_launches++;
     p->ctx->stats.frames_converted += p->n_converted;
@@ -431,7 +472,7 @@ extern "C" int vep_stream_open(vep_ctx *c, int stream_id, int fmt, int w, int h,
     s->out_bytes = ysz * 3;
     s->in_slot = align_up(s->in_bytes, 4096);
     s->out_slot = align_up(kHdrRoom + s->out_bytes + kTrailerRoom, 4096);
-    const int ns = ring_depth + 4;   // ring + one filling + up to two ticks in flight + slack
+    const int ns = ring_depth + VEP_MAX_TICKS_IN_FLIGHT + 2;   // ring + ticks in flight + one filling + slack
     s->slots.resize(ns);
     cudaError_t e = cudaHostAlloc((void **)&s->h_base, (s->in_slot + s->out_slot) * ns, cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_base, (s->in_slot + s->out_slot) * ns);
@@ -515,9 +556,33 @@ extern "C" int vep_commit_input(vep_ctx *c, int stream_id, const vep_frame_meta 
     return VEP_OK;
 }
 
+// Staging copy into pinned memory.  The destination is read next by the GPU's DMA engine, never by
+// this core, so it is written with non-temporal stores: no read-for-ownership traffic and no dirty
+// lines left in the producer core's cache for the H2D copy to snoop (measured on the B200 host:
+// H2D of freshly memcpy'd pinned data ran ~2x slower than from cold pinned memory).
+__attribute__((target("avx2"))) static void stream_copy_avx2(uint8_t *dst, const uint8_t *src, size_t n) {
+    size_t head = (32 - (reinterpret_cast<uintptr_t>(dst) & 31)) & 31;
+    if (head > n) head = n;
+    memcpy(dst, src, head);
+    dst += head; src += head; n -= head;
+    size_t i = 0;
+    for (; i + 128 <= n; i += 128) {
+        const __m256i a = _mm256_loadu_si256((const __m256i *)(src + i)), b = _mm256_loadu_si256((const __m256i *)(src + i + 32));
+        const __m256i c = _mm256_loadu_si256((const __m256i *)(src + i + 64)), d = _mm256_loadu_si256((const __m256i *)(src + i + 96));
+        _mm256_stream_si256((__m256i *)(dst + i), a); _mm256_stream_si256((__m256i *)(dst + i + 32), b);
+        _mm256_stream_si256((__m256i *)(dst + i + 64), c); _mm256_stream_si256((__m256i *)(dst + i + 96), d);
+    }
+    for (; i + 32 <= n; i += 32) _mm256_stream_si256((__m256i *)(dst + i), _mm256_loadu_si256((const __m256i *)(src + i)));
+    memcpy(dst + i, src + i, n - i);
+}
+static void stream_copy(uint8_t *dst, const uint8_t *src, size_t n) {
+    static const bool avx2 = __builtin_cpu_supports("avx2");
+    if (avx2 && n >= 4096) stream_copy_avx2(dst, src, n); else memcpy(dst, src, n);
+}
 static void copy_plane(uint8_t *dst, int dstride, const uint8_t *src, int sstride, int row_bytes, int rows) {
-    if (dstride == sstride && sstride == row_bytes) { memcpy(dst, src, (size_t)row_bytes * rows); return; }
-    for (int r = 0; r < rows; ++r) memcpy(dst + (size_t)r * dstride, src + (size_t)r * sstride, row_bytes);
+    if (dstride == sstride && sstride == row_bytes) stream_copy(dst, src, (size_t)row_bytes * rows);
+    else for (int r = 0; r < rows; ++r) stream_copy(dst + (size_t)r * dstride, src + (size_t)r * sstride, row_bytes);
+    _mm_sfence();   // order the streaming stores before the commit that makes the slot visible
 }
 
 extern "C" int vep_submit(vep_ctx *c, int stream_id, const uint8_t *const plane[3], const int32_t stride[3],
@@ -562,8 +627,8 @@ extern "C" int vep_tick_begin(vep_ctx *c, int *n_frames) {
     if (n_frames) *n_frames = 0;
     DeviceGuard g(c->device);
     std::lock_guard<std::mutex> lk(c->mu);
-    if (c->ticks_in_flight >= 2) return fail(VEP_ERR_BUSY, "two ticks already in flight; call vep_tick_wait");
-    TickRec &t = c->ticks[(c->tick_head + c->ticks_in_flight) % 2];
+    if (c->ticks_in_flight >= VEP_MAX_TICKS_IN_FLIGHT) return fail(VEP_ERR_BUSY, "%d ticks already in flight; call vep_tick_wait", VEP_MAX_TICKS_IN_FLIGHT);
+    TickRec &t = c->ticks[(c->tick_head + c->ticks_in_flight) % VEP_MAX_TICKS_IN_FLIGHT];
     t.slots.clear();
     std::vector<vep_frame_desc> descs;
     std::vector<Stream *> involved;
@@ -637,7 +702,7 @@ extern "C" int vep_tick_wait(vep_ctx *c) {
     }
     t.slots.clear();
     t.active = false;
-    c->tick_head = (c->tick_head + 1) % 2;
+    c->tick_head = (c->tick_head + 1) % VEP_MAX_TICKS_IN_FLIGHT;
     c->ticks_in_flight--;
     return VEP_OK;
 }

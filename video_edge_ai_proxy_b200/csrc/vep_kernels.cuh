@@ -25,13 +25,20 @@ constexpr int kGenericBlocksPerCta = 1024;        // 2x2 blocks per CTA on the g
 
 enum : int { FMT_YUV420P = 0, FMT_YUVJ420P = 1, FMT_NV12 = 2 };
 
-struct __align__(16) FrameDev {   // 64 bytes, one per converted frame, lives in device memory
+enum : int { PATH_GENERIC = 0, PATH_VECTOR = 1, PATH_BULK = 2 };
+
+struct __align__(16) FrameDev {   // 80 bytes, one per converted frame (+1 sentinel), lives in device memory
     const uint8_t *y, *c0, *c1;   // Y, U|UV, V
     uint8_t *dst;
     int32_t sy, sc0, sc1, sd;     // strides in bytes
     int32_t w, h;
     int32_t fmt;
-    int32_t fast;                 // 1: width % 16 == 0 and all pointers/strides vector-aligned
+    int32_t fast;                 // PATH_*: 0 scalar (any even geometry), 1 width%16==0 + vector-aligned,
+                                  //         2 width%32==0 + everything 16-byte aligned (TMA bulk copies)
+    int32_t item_begin;           // first item of this frame in the launch-wide item space (sentinel: total)
+    int32_t segs;                 // 512-px segments per row pair
+    uint32_t segs_magic;          // ceil(2^32 / segs): rp = umulhi(local, magic) for local < 2^20
+    int32_t pad_;
 };
 struct CtaWork {                  // 8 bytes per CTA
     int32_t frame;                // index into the FrameDev table
@@ -165,13 +172,10 @@ __device__ __forceinline__ void luma4_b(uint32_t yw, const ChromaB &P, const Chr
 
 __device__ __forceinline__ uint32_t word_of(const uint4 &v, int i) { return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w; }
 
-// ---- one lane's 16 px x 2 rows, planar ------------------------------------------------------
+// ---- one lane's 16 px x 2 rows, planar: uu/vv hold 8 chroma samples each ---------------------------
 template <bool FULL>
-__device__ __forceinline__ void lane_planar(const FrameDev &f, int rp, int x, uint32_t (&o0)[12], uint32_t (&o1)[12]) {
-    const uint4 ya = ld_stream_v4(f.y + (size_t)(2 * rp) * f.sy + x);
-    const uint4 yb = ld_stream_v4(f.y + (size_t)(2 * rp + 1) * f.sy + x);
-    const uint2 uu = ld_stream_v2(f.c0 + (size_t)rp * f.sc0 + (x >> 1));
-    const uint2 vv = ld_stream_v2(f.c1 + (size_t)rp * f.sc1 + (x >> 1));
+__device__ __forceinline__ void compute_planar(const uint4 &ya, const uint4 &yb, const uint2 &uu, const uint2 &vv,
+                                               uint32_t (&o0)[12], uint32_t (&o1)[12]) {
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
         const uint32_t uw = g < 2 ? uu.x : uu.y, vw = g < 2 ? vv.x : vv.y;
@@ -182,15 +186,18 @@ __device__ __forceinline__ void lane_planar(const FrameDev &f, int rp, int x, ui
         luma4_a<FULL>(word_of(yb, g), P, Q, o1[3 * g], o1[3 * g + 1], o1[3 * g + 2]);
     }
 }
-
-// ---- one lane's 16 px x 2 rows, NV12 (formula C) -----------------------------------------------
-__device__ __forceinline__ void lane_nv12(const FrameDev &f, int rp, int x, uint32_t (&o0)[12], uint32_t (&o1)[12]) {
+template <bool FULL>
+__device__ __forceinline__ void lane_planar(const FrameDev &f, int rp, int x, uint32_t (&o0)[12], uint32_t (&o1)[12]) {
     const uint4 ya = ld_stream_v4(f.y + (size_t)(2 * rp) * f.sy + x);
     const uint4 yb = ld_stream_v4(f.y + (size_t)(2 * rp + 1) * f.sy + x);
-    const int up = rp > 0 ? rp - 1 : 0;
-    const uint4 cu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)rp * f.sc0 + x));   // u0 v0 u1 v1 ...
-    const uint4 pu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)up * f.sc0 + x));   // row above (L2/L1 hit)
-    const bool tail = (rp == (f.h >> 1) - 1);   // rows H-2, H-1: swscale leaves its SIMD output stage
+    const uint2 uu = ld_stream_v2(f.c0 + (size_t)rp * f.sc0 + (x >> 1));
+    const uint2 vv = ld_stream_v2(f.c1 + (size_t)rp * f.sc1 + (x >> 1));
+    compute_planar<FULL>(ya, yb, uu, vv, o0, o1);
+}
+
+// ---- one lane's 16 px x 2 rows, NV12 (formula C): cu = this chroma row, pu = the row above ---------
+__device__ __forceinline__ void compute_nv12(const uint4 &ya, const uint4 &yb, const uint4 &cu, const uint4 &pu, bool tail,
+                                             uint32_t (&o0)[12], uint32_t (&o1)[12]) {
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
         const uint32_t c = word_of(cu, g), p = word_of(pu, g);
@@ -210,6 +217,14 @@ __device__ __forceinline__ void lane_nv12(const FrameDev &f, int rp, int x, uint
             luma4_b(word_of(yb, g), Po, Qo, o1[3 * g], o1[3 * g + 1], o1[3 * g + 2]);
         }
     }
+}
+__device__ __forceinline__ void lane_nv12(const FrameDev &f, int rp, int x, uint32_t (&o0)[12], uint32_t (&o1)[12]) {
+    const uint4 ya = ld_stream_v4(f.y + (size_t)(2 * rp) * f.sy + x);
+    const uint4 yb = ld_stream_v4(f.y + (size_t)(2 * rp + 1) * f.sy + x);
+    const int up = rp > 0 ? rp - 1 : 0;
+    const uint4 cu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)rp * f.sc0 + x));   // u0 v0 u1 v1 ...
+    const uint4 pu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)up * f.sc0 + x));   // row above (L2/L1 hit)
+    compute_nv12(ya, yb, cu, pu, rp == (f.h >> 1) - 1, o0, o1);   // rows H-2, H-1: swscale leaves its SIMD output stage
 }
 
 // ---- generic path: one 2x2 block per step, scalar, any even geometry / alignment ----------------
@@ -269,7 +284,7 @@ yuv_to_bgr24_batched(const FrameDev *__restrict__ frames, const CtaWork *__restr
     const CtaWork cw = work[blockIdx.x];
     const FrameDev f = frames[cw.frame];
 
-    if (!f.fast) {
+    if (f.fast == PATH_GENERIC) {
         const int bw = f.w >> 1, nblk = bw * (f.h >> 1);
         for (int q = cw.first + threadIdx.x; q < min(cw.first + kGenericBlocksPerCta, nblk); q += kThreads)
             generic_block(f, q % bw, q / bw);
@@ -336,6 +351,207 @@ yuv_to_bgr24_batched(const FrameDev *__restrict__ frames, const CtaWork *__restr
             asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         }
     }
+}
+
+
+// ================================================================================================
+// Persistent, TMA-pipelined kernel (the default).
+//
+// Item space: every frame contributes items (bulk/vector path: one item = 2 luma rows x 512 px;
+// generic path: one item = 1024 2x2 blocks); FrameDev::item_begin is the running prefix, with a
+// sentinel entry holding the total.  The grid is sized so that every warp gets the same number of
+// items (host: rounds = ceil(items / resident warps); warps = ceil(items / rounds)), and warp w
+// walks items w, w+G, w+2G, ...  Each warp owns a private pipeline in shared memory:
+//
+//   stage[2] (2 KB each)  <- cp.async.bulk global->shared, completion on a per-stage mbarrier,
+//                            issued by lane 0 TWO items ahead, so DRAM latency is off the warp's
+//                            critical path and no lane spends instructions on load addresses
+//   tile (3 KB)           -> lanes park their 2 x 48 output bytes here (conflict-free 48-B stride),
+//                            lane 0 hands both rows to the TMA unit (cp.async.bulk shared->global),
+//                            which writes full 128-B lines; the read of the tile is awaited just
+//                            before the next item's results are parked, one compute phase later
+//
+// No CTA-wide barrier exists; warps of a CTA never wait for one another.
+// ================================================================================================
+constexpr int kPWarps = 4;                 // warps per CTA
+constexpr int kPThreads = kPWarps * 32;
+constexpr int kStages = 2;
+constexpr int kStageBytes = 2048;          // Y0 512 | Y1 512 | planar: U 256, V 256 | nv12: UV 512, UV-above 512
+constexpr int kWarpSmem = kStages * kStageBytes + 2 * kSegBytes + 128;   // + meta/barrier block = 7296
+constexpr int kPSmemBytes = kPWarps * kWarpSmem;
+
+struct StageMeta {        // 32 bytes, written by lane 0 at issue time, read by all lanes at consume time
+    uint8_t *g0;          // first output row of the item
+    int32_t sd;           // output stride
+    int32_t seg_bytes;    // visible bytes per output row of this item (3 * pixels)
+    int32_t flags;        // bits 0-1 fmt, bit 2 nv12 tail rows, bits 3-4 path
+    int32_t fi;           // frame index
+    int32_t a, b;         // vector path: rp, seg;  generic path: a = first 2x2 block
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (int spins = 0; !done; ++spins) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (!done && spins > (1 << 22)) __trap();   // a lost transaction must fail the launch, not hang the GPU
+    }
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst_smem), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void *dst, uint32_t src_smem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src_smem), "r"(bytes) : "memory");
+}
+
+__global__ void __launch_bounds__(kPThreads)
+yuv_to_bgr24_persistent(const FrameDev *__restrict__ frames, int total_items) {
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint8_t *base = smem_raw + warp * kWarpSmem;
+    uint8_t *tile = base + kStages * kStageBytes;
+    StageMeta *meta = reinterpret_cast<StageMeta *>(tile + 2 * kSegBytes);          // 2 x 32 B
+    const uint32_t bar0 = smem_u32(tile + 2 * kSegBytes + 64);                      // 2 x 8 B
+    const uint32_t stage0 = smem_u32(base), tile_s = smem_u32(tile);
+
+    if (lane == 0) {
+        mbar_init(bar0, 1);
+        mbar_init(bar0 + 8, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+
+    const int G = gridDim.x * kPWarps;
+    const int w0 = blockIdx.x * kPWarps + warp;
+    int fi = 0;   // frames are visited in increasing item order: a running index replaces any search
+
+    // ---- issue: decode item -> (frame, row pair, segment), write the stage's meta, start its loads ----
+    auto issue = [&](int item, int s) {
+        if (item >= total_items) return;
+        while (item >= __ldg(&frames[fi + 1].item_begin)) ++fi;
+        const FrameDev *f = frames + fi;
+        const int4 q2 = __ldg(reinterpret_cast<const int4 *>(&f->w));           // w, h, fmt, path
+        const int4 q3 = __ldg(reinterpret_cast<const int4 *>(&f->item_begin));  // item_begin, segs, magic
+        const int w = q2.x, h = q2.y, fmt = q2.z, path = q2.w;
+        const int local = item - q3.x;
+        if (path == PATH_GENERIC) {
+            if (lane == 0) { meta[s].flags = fmt | (path << 3); meta[s].fi = fi; meta[s].a = local * kGenericBlocksPerCta; }
+            return;
+        }
+        const int segs = q3.y;
+        const int rp = q3.z ? (int)__umulhi((uint32_t)local, (uint32_t)q3.z) : local;   // magic 0 <=> one segment per row
+        const int seg = local - rp * segs;
+        const int wseg = min(kSegPx, w - seg * kSegPx);
+        const int tail = (fmt == FMT_NV12 && rp == (h >> 1) - 1) ? 1 : 0;
+        if (lane == 0) {
+            const int4 q1 = __ldg(reinterpret_cast<const int4 *>(&f->sy));      // sy, sc0, sc1, sd
+            uint8_t *dst = const_cast<uint8_t *>(reinterpret_cast<const uint8_t *>(__ldg(reinterpret_cast<const unsigned long long *>(&f->dst))));
+            meta[s].g0 = dst + (size_t)(2 * rp) * q1.w + (size_t)seg * kSegBytes;
+            meta[s].sd = q1.w;
+            meta[s].seg_bytes = 3 * wseg;
+            meta[s].flags = fmt | (tail << 2) | (path << 3);
+            meta[s].fi = fi; meta[s].a = rp; meta[s].b = seg;
+            if (path == PATH_BULK) {
+                const uint8_t *y = reinterpret_cast<const uint8_t *>(__ldg(reinterpret_cast<const unsigned long long *>(&f->y)));
+                const uint8_t *c0 = reinterpret_cast<const uint8_t *>(__ldg(reinterpret_cast<const unsigned long long *>(&f->c0)));
+                const uint32_t bar = bar0 + 8 * s, st = stage0 + s * kStageBytes;
+                const uint8_t *yr = y + (size_t)(2 * rp) * q1.x + seg * kSegPx;
+                if (fmt == FMT_NV12) {
+                    mbar_expect_tx(bar, 4 * wseg);
+                    bulk_g2s(st, yr, wseg, bar);
+                    bulk_g2s(st + 512, yr + q1.x, wseg, bar);
+                    bulk_g2s(st + 1024, c0 + (size_t)rp * q1.y + seg * kSegPx, wseg, bar);
+                    bulk_g2s(st + 1536, c0 + (size_t)(rp > 0 ? rp - 1 : 0) * q1.y + seg * kSegPx, wseg, bar);
+                } else {
+                    const uint8_t *c1 = reinterpret_cast<const uint8_t *>(__ldg(reinterpret_cast<const unsigned long long *>(&f->c1)));
+                    mbar_expect_tx(bar, 3 * wseg);
+                    bulk_g2s(st, yr, wseg, bar);
+                    bulk_g2s(st + 512, yr + q1.x, wseg, bar);
+                    bulk_g2s(st + 1024, c0 + (size_t)rp * q1.y + seg * (kSegPx / 2), wseg / 2, bar);
+                    bulk_g2s(st + 1280, c1 + (size_t)rp * q1.z + seg * (kSegPx / 2), wseg / 2, bar);
+                }
+            }
+        }
+    };
+
+    issue(w0, 0);
+    issue(w0 + G, 1);
+    __syncwarp();
+    uint32_t phase = 0;   // bit s = parity to wait for on stage s
+
+    int k = 0;
+    for (int item = w0; item < total_items; item += G, ++k) {
+        const int s = k & 1;
+        const StageMeta m = meta[s];            // broadcast read
+        const int fmt = m.flags & 3, path = (m.flags >> 3) & 3;
+        const uint8_t *st = base + s * kStageBytes;
+
+        if (path == PATH_GENERIC) {
+            const FrameDev f = frames[m.fi];
+            const int bw = f.w >> 1, nblk = bw * (f.h >> 1);
+            for (int q = m.a + lane; q < min(m.a + kGenericBlocksPerCta, nblk); q += 32) generic_block(f, q % bw, q / bw);
+            __syncwarp();
+            issue(item + kStages * G, s);
+            __syncwarp();
+            continue;
+        }
+
+        uint32_t o0[12], o1[12];
+        const bool active = lane * 48 < m.seg_bytes;
+        if (path == PATH_BULK) {
+            mbar_wait(bar0 + 8 * s, (phase >> s) & 1);
+            phase ^= 1u << s;
+            if (active) {
+                const uint4 ya = *reinterpret_cast<const uint4 *>(st + lane * 16);
+                const uint4 yb = *reinterpret_cast<const uint4 *>(st + 512 + lane * 16);
+                if (fmt == FMT_NV12) {
+                    const uint4 cu = *reinterpret_cast<const uint4 *>(st + 1024 + lane * 16);
+                    const uint4 pu = *reinterpret_cast<const uint4 *>(st + 1536 + lane * 16);
+                    compute_nv12(ya, yb, cu, pu, (m.flags >> 2) & 1, o0, o1);
+                } else {
+                    const uint2 uu = *reinterpret_cast<const uint2 *>(st + 1024 + lane * 8);
+                    const uint2 vv = *reinterpret_cast<const uint2 *>(st + 1280 + lane * 8);
+                    if (fmt == FMT_YUV420P) compute_planar<false>(ya, yb, uu, vv, o0, o1);
+                    else compute_planar<true>(ya, yb, uu, vv, o0, o1);
+                }
+            }
+        } else if (active) {   // PATH_VECTOR: per-lane loads straight from global (width % 32 != 0 or 8-byte aligned chroma)
+            const FrameDev f = frames[m.fi];
+            const int x = m.b * kSegPx + lane * 16;
+            if (fmt == FMT_YUV420P) lane_planar<false>(f, m.a, x, o0, o1);
+            else if (fmt == FMT_YUVJ420P) lane_planar<true>(f, m.a, x, o0, o1);
+            else lane_nv12(f, m.a, x, o0, o1);
+        }
+        __syncwarp();                          // every lane has consumed stage s (and its meta)
+        issue(item + kStages * G, s);          // refill it two items ahead
+
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // previous item's tile has been read out
+        __syncwarp();
+        if (active) {
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                *reinterpret_cast<uint4 *>(tile + lane * 48 + j * 16) = make_uint4(o0[4 * j], o0[4 * j + 1], o0[4 * j + 2], o0[4 * j + 3]);
+                *reinterpret_cast<uint4 *>(tile + kSegBytes + lane * 48 + j * 16) = make_uint4(o1[4 * j], o1[4 * j + 1], o1[4 * j + 2], o1[4 * j + 3]);
+            }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the TMA unit
+        __syncwarp();
+        if (lane == 0) {
+            bulk_s2g(m.g0, tile_s, m.seg_bytes);
+            bulk_s2g(m.g0 + m.sd, tile_s + kSegBytes, m.seg_bytes);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // all output bytes have left shared memory
 }
 
 }  // namespace vep
