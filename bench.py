@@ -43,6 +43,7 @@ WORKLOADS = {
     "16x1080p": (16, "yuv420p", 1920, 1080, "16 synthetic 1080p yuv420p cameras per GPU, one batched launch per tick (BASELINE configs[1])"),
     "8x1080p": (8, "yuv420p", 1920, 1080, "8 synthetic 1080p yuv420p cameras per GPU (BASELINE configs[2] layout: 64 cameras over 8 GPUs)"),
     "8x4k-nv12": (8, "nv12", 3840, 2160, "8 synthetic 3840x2160 NV12 cameras per GPU (BASELINE configs[3] frames)"),
+    "64x1080p": (64, "yuv420p", 1920, 1080, "64 synthetic 1080p yuv420p cameras on one GPU (launch-overhead study, not a BASELINE config)"),
     "1x480p": (1, "yuv420p", 640, 480, "one 640x480 yuv420p stream (BASELINE configs[0])"),
 }
 
@@ -314,8 +315,9 @@ def run_gpu(args):
     torch.cuda.synchronize(dev)
     w0 = time.perf_counter()
     e0.record(stream)
+    overlapped = not args.strict_order     # consecutive ticks use disjoint buffer sets -> may overlap
     for i in range(args.steps):
-        plans[i % n_sets].launch(sptr)
+        plans[i % n_sets].launch(sptr, overlapped)
     e1.record(stream)
     torch.cuda.synchronize(dev)
     w1 = time.perf_counter()
@@ -381,10 +383,11 @@ def run_gpu(args):
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {desc}", "frames_per_step_per_gpu": n, "format": fmt, "width": w, "height": h,
                    "l2": f"inputs/outputs rotate over {n_sets} buffer sets of {per_set_bytes / 1e6:.0f} MB (> {l2_bytes / 1e6:.0f} MB L2)",
-                   "parallelism": f"cameras sharded {n}/GPU, no collective", "kernel": os.environ.get("VEP_KERNEL", "oneshot")},
+                   "parallelism": f"cameras sharded {n}/GPU, no collective", "kernel": os.environ.get("VEP_KERNEL", "tick"),
+                   "launch": "strict stream order" if args.strict_order else "vep_plan_launch_overlapped: consecutive ticks touch disjoint buffer sets"},
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
                      "traffic": None, "peak_source": peak_src, "frac_of_nominal_8TBs": round(achieved / 8000.0, 4),
-                     "alg_bytes_per_launch": per_set_bytes, "kernel": "vep::yuv_to_bgr24_persistent" if os.environ.get("VEP_KERNEL", "oneshot") == "persistent" else "vep::yuv_to_bgr24_batched"},
+                     "alg_bytes_per_launch": per_set_bytes, "kernel": {"persistent": "vep::yuv_to_bgr24_persistent", "oneshot": "vep::yuv_to_bgr24_batched"}.get(os.environ.get("VEP_KERNEL", "tick"), "vep::yuv_to_bgr24_tick")},
         "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d_per_step), "d2h_bytes_per_step": int(d2h_per_step),
                 "steps": e2e_steps, "api": "FramePath.submit (host planes -> pinned staging) + tick_begin/tick_wait (3 ticks in flight) + result_packed",
                 "pcie_gbs": round((h2d_per_step + d2h_per_step) * e2e_steps / e2e_s / 1e9, 2), "message_bytes": msg_bytes},
@@ -423,6 +426,7 @@ def main():
     ap.add_argument("--sets", type=int, default=9, help="minimum number of rotating buffer sets")
     ap.add_argument("--e2e-steps", type=int, default=60)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--strict-order", action="store_true", help="launch every tick fully ordered after the previous one (no overlap)")
     args = ap.parse_args()
     if args.impl == "reference":
         # the CPU arm times one tick per step as well; cap so the run ends within minutes

@@ -90,6 +90,11 @@ void vep_destroy(vep_ctx *ctx);
 int vep_convert_batch(vep_ctx *ctx, const vep_frame_desc *descs, int n, void *cuda_stream);
 int vep_plan_create(vep_ctx *ctx, const vep_frame_desc *descs, int n, vep_plan **out);
 int vep_plan_launch(vep_plan *plan, void *cuda_stream);
+/* Same launch, but the caller asserts that it neither reads nor overwrites anything the PREVIOUS
+ * kernel launch on this stream writes (e.g. consecutive ticks over disjoint buffer sets).  The GPU may
+ * then start this launch while the previous one is still draining; ordering against everything
+ * else on the stream (copies, events, other kernels) is unchanged.  Results are identical. */
+int vep_plan_launch_overlapped(vep_plan *plan, void *cuda_stream);
 /* frames with convert!=0, CTAs per launch, algorithmic bytes (4.5*W*H per converted frame) */
 int vep_plan_info(const vep_plan *plan, int *n_converted, int *n_ctas, int64_t *alg_bytes);
 void vep_plan_destroy(vep_plan *plan);

@@ -211,6 +211,86 @@ def test_persistent_tma_kernel_bit_identical(golden_pixels, small_frames):
             os.environ["VEP_KERNEL"] = old
 
 
+def _with_env(env):
+    class _Ctx:
+        def __enter__(self_):
+            self_.old = {k: os.environ.get(k) for k in env}
+            os.environ.update(env)
+
+        def __exit__(self_, *a):
+            for k, v in self_.old.items():
+                if v is None:
+                    os.environ.pop(k, None)
+                else:
+                    os.environ[k] = v
+    return _Ctx()
+
+
+@pytest.mark.parametrize("env", [{"VEP_RPT": "1", "VEP_MINB": "5"}, {"VEP_RPT": "1", "VEP_MINB": "6"}, {"VEP_RPT": "1", "VEP_MINB": "8"},
+                                 {"VEP_RPT": "2", "VEP_MINB": "3"}, {"VEP_RPT": "2", "VEP_MINB": "4"}, {"VEP_KERNEL": "oneshot"}])
+def test_tick_kernel_variants_bit_identical(env, small_frames):
+    with _with_env(env), FramePath(0) as p:
+        for fmt, w, h, seed, planes, want in small_frames:
+            assert np.array_equal(gpu_convert(p, fmt, planes), want), (env, fmt, w, h)
+        for fmt, w, h in (("yuv420p", 1920, 1080), ("nv12", 1920, 1080), ("yuvj420p", 640, 480), ("yuv420p", 528, 6), ("nv12", 1040, 10),
+                          ("yuv420p", 16, 2), ("nv12", 3840, 2160), ("yuv420p", 642, 482), ("nv12", 64, 14)):
+            planes = make_planes(fmt, w, h, w + h)
+            assert np.array_equal(gpu_convert(p, fmt, planes), F.to_bgr24(fmt, planes)), (env, fmt, w, h)
+        # 40 frames in one launch (128-entry parameter table) and 150 frames (falls back to the device table)
+        for n in (40, 150):
+            descs, keep = [], []
+            for i in range(n):
+                fmt, w, h = (("yuv420p", 320, 240), ("nv12", 352, 288), ("yuvj420p", 160, 120), ("yuv420p", 50, 6))[i % 4]
+                planes = make_planes(fmt, w, h, i)
+                t = [torch.from_numpy(q).cuda() for q in planes]
+                out = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+                descs.append(desc_from_tensors(fmt, t, out))
+                keep.append((fmt, planes, t, out))
+            p.convert_batch(descs, torch.cuda.current_stream().cuda_stream)
+            torch.cuda.synchronize()
+            for fmt, planes, t, out in keep:
+                assert np.array_equal(out.cpu().numpy(), F.to_bgr24(fmt, planes)), (env, n, fmt)
+
+
+def test_overlapped_and_ordered_launches(path):
+    """Back-to-back launches: overlapped ones over disjoint buffers stay exact; ordered ones that
+    re-use one output buffer leave the LAST launch's result (stream order is kept)."""
+    st = torch.cuda.current_stream().cuda_stream
+    sets = []
+    for s in range(6):
+        planes = [make_planes("yuv420p", 1920, 1080, 10 * s + i) for i in range(4)]
+        descs, outs = [], []
+        for pl in planes:
+            t = [torch.from_numpy(q).cuda() for q in pl]
+            out = torch.zeros((1080, 1920, 3), dtype=torch.uint8, device="cuda")
+            descs.append(desc_from_tensors("yuv420p", t, out))
+            outs.append((t, out))
+        sets.append((planes, outs, path.plan(descs)))
+    for _ in range(3):
+        for planes, outs, plan in sets:
+            plan.launch(st, overlapped=True)
+    torch.cuda.synchronize()
+    for planes, outs, plan in sets:
+        for pl, (_, out) in zip(planes, outs):
+            assert np.array_equal(out.cpu().numpy(), F.to_bgr24("yuv420p", pl))
+    # ordered: 6 different inputs into ONE output buffer, default launch
+    shared = torch.zeros((1080, 1920, 3), dtype=torch.uint8, device="cuda")
+    plans, keep = [], []
+    for s in range(6):
+        pl = make_planes("yuv420p", 1920, 1080, 100 + s)
+        t = [torch.from_numpy(q).cuda() for q in pl]
+        keep.append((pl, t))
+        plans.append(path.plan([desc_from_tensors("yuv420p", t, shared)]))
+    for pln in plans:
+        pln.launch(st)
+    torch.cuda.synchronize()
+    assert np.array_equal(shared.cpu().numpy(), F.to_bgr24("yuv420p", keep[-1][0]))
+    for _, _, pln in sets:
+        pln.close()
+    for pln in plans:
+        pln.close()
+
+
 def test_all_store_modes_bit_identical():
     planes = make_planes("yuv420p", 1920, 1080, 42)
     want = F.to_bgr24("yuv420p", planes)
@@ -220,10 +300,12 @@ def test_all_store_modes_bit_identical():
     try:
         for mode in ("0", "1", "2"):
             os.environ["VEP_STORE_MODE"] = mode
+            os.environ["VEP_KERNEL"] = "oneshot"
             with FramePath(0) as p:
                 assert np.array_equal(gpu_convert(p, "yuv420p", planes), want), mode
                 assert np.array_equal(gpu_convert(p, "nv12", nv), want_nv), mode
     finally:
+        os.environ.pop("VEP_KERNEL", None)
         if old is None:
             os.environ.pop("VEP_STORE_MODE", None)
         else:

@@ -54,6 +54,7 @@ SIGNATURES = {
     "vep_convert_batch": (_i, [_p, C.POINTER(FrameDesc), _i, _p]),
     "vep_plan_create": (_i, [_p, C.POINTER(FrameDesc), _i, _pp]),
     "vep_plan_launch": (_i, [_p, _p]),
+    "vep_plan_launch_overlapped": (_i, [_p, _p]),
     "vep_plan_info": (_i, [_p, _ip, _ip, C.POINTER(C.c_int64)]),
     "vep_plan_destroy": (None, [_p]),
     "vep_stream_open": (_i, [_p, _i, _i, _i, _i, _i]),

@@ -76,17 +76,20 @@ struct Tables {
     int64_t alg_bytes = 0;
     int n_converted = 0;
     int total_items = 0;            // item space of the persistent kernel
+    std::vector<int32_t> tick_cta_begin;   // tick kernel: first CTA of each frame, then the grid size
 };
 
 static inline bool aligned(const void *p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
 
-static int build_tables(const vep_frame_desc *d, int n, Tables &t) {
+static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1) {
     if (n < 0 || (n > 0 && !d)) return fail(VEP_ERR_INVALID_ARG, "descs is null or n < 0");
     t.frames.clear();
     t.work.clear();
     t.alg_bytes = 0;
     t.n_converted = 0;
     t.total_items = 0;
+    t.tick_cta_begin.clear();
+    int tick_ctas = 0;
     for (int i = 0; i < n; ++i) {
         const vep_frame_desc &s = d[i];
         if (!s.convert) continue;
@@ -115,6 +118,9 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t) {
         const int fi = (int)t.frames.size();
         t.frames.push_back(f);
         int items;
+        t.tick_cta_begin.push_back(tick_ctas);
+        if (f.fast != vep::PATH_GENERIC) tick_ctas += (f.segs * ((h / 2 + rpt - 1) / rpt) + vep::kWarpsPerCta - 1) / vep::kWarpsPerCta;
+        else tick_ctas += ((w / 2) * (h / 2) + vep::kGenericBlocksPerCta - 1) / vep::kGenericBlocksPerCta;
         if (f.fast != vep::PATH_GENERIC) {
             items = f.segs * (h / 2);
             for (int it = 0; it < items; it += vep::kWarpsPerCta) t.work.push_back(CtaWork{fi, it});
@@ -131,6 +137,7 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t) {
     FrameDev sentinel{};
     sentinel.item_begin = t.total_items;
     t.frames.push_back(sentinel);
+    t.tick_cta_begin.push_back(tick_ctas);
     return VEP_OK;
 }
 
@@ -181,7 +188,10 @@ struct TickRec {
 
 struct vep_ctx {
     int device = 0;
-    int kernel = 1;              // 1: one-shot CTA-per-tile (default), 0: persistent TMA-pipelined (VEP_KERNEL=persistent)
+    int kernel = 2;              // 2: tick kernel, table in kernel params (default); 1: table-driven one-shot
+                                 // (VEP_KERNEL=oneshot; also the fallback beyond 128 frames); 0: VEP_KERNEL=persistent
+    int rpt = 2, minb = 4;       // tick kernel variant: row pairs per lane, min CTAs/SM (VEP_RPT, VEP_MINB)
+    int pdl = 1;                 // programmatic dependent launch attribute on tick launches (VEP_PDL=0 disables)
     int store_mode = 0;          // one-shot kernel only (VEP_STORE_MODE)
     int resident_warps = 0;      // persistent kernel: warps the whole GPU keeps resident
     cudaStream_t main = nullptr;
@@ -193,6 +203,7 @@ struct vep_ctx {
     int tick_head = 0, ticks_in_flight = 0;         // oldest in flight = tick_head
     vep_stats stats{};
     Tables scratch;
+    std::vector<uint8_t> tick_blob;
 };
 
 struct vep_plan {
@@ -200,6 +211,8 @@ struct vep_plan {
     FrameDev *d_frames = nullptr;
     CtaWork *d_work = nullptr;
     int n_ctas = 0, n_converted = 0, total_items = 0;
+    std::vector<uint8_t> tick_blob, tick_blob_overlap;   // TickParams<16|128> (wait_prior = 1 | 0), passed by value
+    int tick_cap = 0, tick_grid = 0;
     int64_t alg_bytes = 0;
 };
 
@@ -214,6 +227,51 @@ static int persistent_ctas(const vep_ctx *c, int total_items) {
     const int rounds = (total_items + c->resident_warps - 1) / c->resident_warps;
     const int warps = (total_items + rounds - 1) / rounds;
     return (warps + vep::kPWarps - 1) / vep::kPWarps;
+}
+
+// ---- tick kernel: descriptor table travels as a kernel parameter -------------------------------------
+static constexpr int kTickCapSmall = 16, kTickCapLarge = 128;
+
+template <int NF>
+static void fill_tick(const Tables &t, std::vector<uint8_t> &blob) {
+    blob.assign(sizeof(vep::TickParams<NF>), 0);
+    auto *P = reinterpret_cast<vep::TickParams<NF> *>(blob.data());
+    const int n = t.n_converted;
+    P->n_frames = n;
+    P->wait_prior = 1;
+    for (int i = 0; i <= n; ++i) P->cta_begin[i] = t.tick_cta_begin[i];
+    for (int i = 0; i < n; ++i) P->frames[i] = t.frames[i];
+}
+// returns capacity used (0: does not fit -> caller falls back to the table-driven kernel)
+static int make_tick_blob(const Tables &t, std::vector<uint8_t> &blob, int *grid) {
+    const int n = t.n_converted;
+    *grid = n ? t.tick_cta_begin[n] : 0;
+    if (n <= kTickCapSmall) { fill_tick<kTickCapSmall>(t, blob); return kTickCapSmall; }
+    if (n <= kTickCapLarge) { fill_tick<kTickCapLarge>(t, blob); return kTickCapLarge; }
+    return 0;
+}
+template <int NF>
+static const void *tick_kernel(int rpt, int minb) {
+    if (rpt == 2) return minb >= 4 ? (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4> : (const void *)vep::yuv_to_bgr24_tick<NF, 2, 3>;
+    if (minb >= 8) return (const void *)vep::yuv_to_bgr24_tick<NF, 1, 8>;
+    if (minb >= 6) return (const void *)vep::yuv_to_bgr24_tick<NF, 1, 6>;
+    return (const void *)vep::yuv_to_bgr24_tick<NF, 1, 5>;
+}
+static int launch_tick(const vep_ctx *c, int cap, const std::vector<uint8_t> &blob, int grid, cudaStream_t st) {
+    if (grid <= 0) return VEP_OK;
+    const void *fn = cap == kTickCapSmall ? tick_kernel<kTickCapSmall>(c->rpt, c->minb) : tick_kernel<kTickCapLarge>(c->rpt, c->minb);
+    void *args[1] = {const_cast<uint8_t *>(blob.data())};
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(vep::kThreads);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = c->pdl ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    CUDA_TRY(cudaLaunchKernelExC(&cfg, fn, args));
+    return VEP_OK;
 }
 
 static int launch_tables(const vep_ctx *c, const FrameDev *d_frames, const CtaWork *d_work, int n_ctas, int total_items, cudaStream_t st) {
@@ -250,7 +308,12 @@ extern "C" int vep_create(int device, vep_ctx **out) {
     c->store_mode = sm ? atoi(sm) : 0;
     if (c->store_mode < 0 || c->store_mode > 2) c->store_mode = 0;
     const char *kn = getenv("VEP_KERNEL");
-    c->kernel = (kn && strcmp(kn, "persistent") == 0) ? 0 : 1;   // default: one-shot (the faster one)
+    c->kernel = !kn ? 2 : strcmp(kn, "persistent") == 0 ? 0 : strcmp(kn, "oneshot") == 0 ? 1 : 2;
+    const char *er = getenv("VEP_RPT"), *em = getenv("VEP_MINB");
+    c->rpt = (er && atoi(er) == 1) ? 1 : 2;
+    c->minb = em ? atoi(em) : (c->rpt == 2 ? 4 : 6);
+    const char *ep = getenv("VEP_PDL");
+    c->pdl = (ep && atoi(ep) == 0) ? 0 : 1;
     CUDA_TRY(cudaFuncSetAttribute(vep::yuv_to_bgr24_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, vep::kPSmemBytes));
     CUDA_TRY(cudaFuncSetAttribute(vep::yuv_to_bgr24_persistent, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     int per_sm = 0;
@@ -291,6 +354,16 @@ extern "C" void vep_destroy(vep_ctx *c) {
 // upload `t` through the next ring buffer and launch on `st`
 static int upload_and_launch(vep_ctx *c, const Tables &t, cudaStream_t st) {
     if (t.total_items == 0) return VEP_OK;
+    if (c->kernel == 2) {
+        int grid = 0;
+        const int cap = make_tick_blob(t, c->tick_blob, &grid);
+        if (cap) {   // cudaLaunchKernel copies the parameter block before returning: the blob is reusable at once
+            int rc = launch_tick(c, cap, c->tick_blob, grid, st);
+            if (rc) return rc;
+            c->stats.kernel_launches++;
+            return VEP_OK;
+        }
+    }
     TableBuf &b = c->tb[c->tb_next];
     c->tb_next = (c->tb_next + 1) % 4;
     if (b.pending) { CUDA_TRY(cudaEventSynchronize(b.used)); b.pending = false; }
@@ -321,7 +394,7 @@ extern "C" int vep_convert_batch(vep_ctx *c, const vep_frame_desc *descs, int n,
     if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
     DeviceGuard g(c->device);
     std::lock_guard<std::mutex> lk(c->mu);
-    int rc = build_tables(descs, n, c->scratch);
+    int rc = build_tables(descs, n, c->scratch, c->rpt);
     if (rc) return rc;
     rc = upload_and_launch(c, c->scratch, (cudaStream_t)cuda_stream);
     if (rc) return rc;
@@ -334,7 +407,7 @@ extern "C" int vep_plan_create(vep_ctx *c, const vep_frame_desc *descs, int n, v
     *out = nullptr;
     DeviceGuard g(c->device);
     Tables t;
-    int rc = build_tables(descs, n, t);
+    int rc = build_tables(descs, n, t, c->rpt);
     if (rc) return rc;
     vep_plan *p = new (std::nothrow) vep_plan();
     if (!p) return fail(VEP_ERR_NOMEM, "out of host memory");
@@ -342,6 +415,15 @@ extern "C" int vep_plan_create(vep_ctx *c, const vep_frame_desc *descs, int n, v
     p->n_ctas = c->kernel == 0 ? (t.total_items ? persistent_ctas(c, t.total_items) : 0) : (int)t.work.size();
     p->total_items = t.total_items;
     p->n_converted = t.n_converted;
+    if (c->kernel == 2) {
+        p->tick_cap = make_tick_blob(t, p->tick_blob, &p->tick_grid);
+        if (p->tick_cap) {
+            p->n_ctas = p->tick_grid;
+            p->tick_blob_overlap = p->tick_blob;
+            reinterpret_cast<int32_t *>(p->tick_blob_overlap.data())[1] = 0;   // TickParams::wait_prior
+        }
+        else p->n_ctas = (int)t.work.size();
+    }
     p->alg_bytes = t.alg_bytes;
     if (t.total_items) {
         cudaError_t e = cudaMalloc(&p->d_frames, t.frames.size() * sizeof(FrameDev));
@@ -359,15 +441,18 @@ extern "C" int vep_plan_create(vep_ctx *c, const vep_frame_desc *descs, int n, v
     return VEP_OK;
 }
 
-extern "C" int vep_plan_launch(vep_plan *p, void *cuda_stream) {
+static int plan_launch(vep_plan *p, void *cuda_stream, bool overlap) {
     if (!p) return fail(VEP_ERR_INVALID_ARG, "plan is null");
     DeviceGuard g(p->ctx->device);
-    int rc = launch_tables(p->ctx, p->d_frames, p->d_work, p->n_ctas, p->total_items, (cudaStream_t)cuda_stream);
+    int rc = p->tick_cap ? launch_tick(p->ctx, p->tick_cap, overlap ? p->tick_blob_overlap : p->tick_blob, p->tick_grid, (cudaStream_t)cuda_stream)
+                         : launch_tables(p->ctx, p->d_frames, p->d_work, p->n_ctas, p->total_items, (cudaStream_t)cuda_stream);
     if (rc) return rc;
     p->ctx->stats.kernel_launches++;
     p->ctx->stats.frames_converted += p->n_converted;
     return VEP_OK;
 }
+extern "C" int vep_plan_launch(vep_plan *p, void *cuda_stream) { return plan_launch(p, cuda_stream, false); }
+extern "C" int vep_plan_launch_overlapped(vep_plan *p, void *cuda_stream) { return plan_launch(p, cuda_stream, true); }
 
 extern "C" int vep_plan_info(const vep_plan *p, int *n_converted, int *n_ctas, int64_t *alg_bytes) {
     if (!p) return fail(VEP_ERR_INVALID_ARG, "plan is null");
@@ -663,7 +748,7 @@ extern "C" int vep_tick_begin(vep_ctx *c, int *n_frames) {
     }
     if (t.slots.empty()) return VEP_OK;
     // 2. one batched launch for the whole tick
-    int rc = build_tables(descs.data(), (int)descs.size(), c->scratch);
+    int rc = build_tables(descs.data(), (int)descs.size(), c->scratch, c->rpt);
     if (rc) return rc;
     CUDA_TRY(cudaEventRecord(t.k0, c->main));
     rc = upload_and_launch(c, c->scratch, c->main);

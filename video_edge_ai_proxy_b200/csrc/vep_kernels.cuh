@@ -355,6 +355,120 @@ yuv_to_bgr24_batched(const FrameDev *__restrict__ frames, const CtaWork *__restr
 
 
 // ================================================================================================
+// Tick kernel (the default): descriptor table in the kernel-parameter constant bank.
+//
+// Same tiling as the table-driven kernel above (one warp = 512 px x 2 luma rows per row pair,
+// shared-memory re-order, 16-byte warp-contiguous stores) but nothing on a CTA's critical path
+// waits for global memory before its pixel loads are issued: the frame descriptors and the
+// CTA->frame prefix arrive with the launch itself (__grid_constant__), the CTA finds its frame with
+// independent constant-bank reads, and row pair / segment come from a multiply-high.  With RPT = 2
+// a lane converts two vertically adjacent row pairs: all eight loads are in flight before the
+// first multiply, and NV12 re-uses the first pair's chroma row as the "row above" of the second.
+// ================================================================================================
+template <int NF>
+struct TickParams {
+    int32_t n_frames;
+    int32_t wait_prior;      // 1: griddepcontrol.wait before touching memory (ordinary stream order);
+                             // 0: the caller declared this launch independent of the previous kernel
+    int32_t pad_[2];
+    int32_t cta_begin[(NF + 1 + 3) / 4 * 4];   // cta_begin[f] = first CTA of frame f; [n_frames] = grid size
+    FrameDev frames[NF];
+};
+
+template <int NF, int RPT, int MINB>
+__global__ void __launch_bounds__(kThreads, MINB)
+yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
+    __shared__ __align__(128) uint8_t tile[kWarpsPerCta][2][kSegBytes];
+    // Programmatic dependent launch: let the next launch on this stream start filling SMs as this
+    // one drains (a 16-frame tick lasts ~27 us, of which ~4 us are ramp and tail); unless the caller
+    // vouched for independence, wait here until the previous kernel's writes are complete.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (p.wait_prior) asm volatile("griddepcontrol.wait;" ::: "memory");
+    const int cta = blockIdx.x;
+    int fi = 0;
+    if (NF <= 16) {
+#pragma unroll
+        for (int i = 1; i < NF; ++i) fi += (i < p.n_frames && cta >= p.cta_begin[i]) ? 1 : 0;   // independent constant reads
+    } else {
+        int lo = 0, hi = p.n_frames - 1;
+        while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (cta >= p.cta_begin[mid]) lo = mid; else hi = mid - 1; }
+        fi = lo;
+    }
+    const FrameDev &f = p.frames[fi];
+    const int first = (cta - p.cta_begin[fi]) * (f.fast == PATH_GENERIC ? kGenericBlocksPerCta : kWarpsPerCta);
+
+    if (f.fast == PATH_GENERIC) {
+        const int bw = f.w >> 1, nblk = bw * (f.h >> 1);
+        for (int q = first + threadIdx.x; q < min(first + kGenericBlocksPerCta, nblk); q += kThreads)
+            generic_block(f, q % bw, q / bw);
+        return;
+    }
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int segs = f.segs, hp = f.h >> 1;
+    const int groups = (hp + RPT - 1) / RPT;               // row-pair groups per segment column
+    const int item = first + warp;
+    if (item >= segs * groups) return;                      // warp-uniform
+    const int grp = f.segs_magic ? (int)__umulhi((uint32_t)item, f.segs_magic) : item;
+    const int seg = item - grp * segs;
+    const int rp0 = grp * RPT;
+    const int x = seg * kSegPx + lane * 16;
+    const bool active = x < f.w;
+    const int seg_bytes = min(kSegPx, f.w - seg * kSegPx) * 3;   // multiple of 48
+    uint8_t *t0 = tile[warp][0], *t1 = tile[warp][1];
+
+    // ---- all loads first ----
+    uint4 ya[RPT], yb[RPT], ca[RPT];   // ca: planar {U.lo,U.hi,V.lo,V.hi}; nv12: the 16 interleaved chroma bytes
+    uint4 pu = make_uint4(0, 0, 0, 0);
+    const bool nv12 = f.fmt == FMT_NV12;
+    if (active) {
+#pragma unroll
+        for (int r = 0; r < RPT; ++r) {
+            const int rp = min(rp0 + r, hp - 1);            // clamp: an odd tail group re-reads the last pair (not stored)
+            ya[r] = ld_stream_v4(f.y + (size_t)(2 * rp) * f.sy + x);
+            yb[r] = ld_stream_v4(f.y + (size_t)(2 * rp + 1) * f.sy + x);
+            if (nv12) {
+                ca[r] = ld_stream_v4(f.c0 + (size_t)rp * f.sc0 + x);
+            } else {
+                const uint2 uu = ld_stream_v2(f.c0 + (size_t)rp * f.sc0 + (x >> 1));
+                const uint2 vv = ld_stream_v2(f.c1 + (size_t)rp * f.sc1 + (x >> 1));
+                ca[r] = make_uint4(uu.x, uu.y, vv.x, vv.y);
+            }
+        }
+        if (nv12) pu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)(rp0 > 0 ? rp0 - 1 : 0) * f.sc0 + x));
+    }
+
+#pragma unroll
+    for (int r = 0; r < RPT; ++r) {
+        const int rp = rp0 + r;
+        if (rp >= hp) break;                                // warp-uniform
+        if (active) {
+            uint32_t o0[12], o1[12];
+            if (f.fmt == FMT_YUV420P) compute_planar<false>(ya[r], yb[r], make_uint2(ca[r].x, ca[r].y), make_uint2(ca[r].z, ca[r].w), o0, o1);
+            else if (f.fmt == FMT_YUVJ420P) compute_planar<true>(ya[r], yb[r], make_uint2(ca[r].x, ca[r].y), make_uint2(ca[r].z, ca[r].w), o0, o1);
+            else compute_nv12(ya[r], yb[r], ca[r], r == 0 ? pu : ca[r > 0 ? r - 1 : 0], rp == hp - 1, o0, o1);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {   // 48 B lane stride: conflict-free per quarter warp
+                *reinterpret_cast<uint4 *>(t0 + lane * 48 + k * 16) = make_uint4(o0[4 * k], o0[4 * k + 1], o0[4 * k + 2], o0[4 * k + 3]);
+                *reinterpret_cast<uint4 *>(t1 + lane * 48 + k * 16) = make_uint4(o1[4 * k], o1[4 * k + 1], o1[4 * k + 2], o1[4 * k + 3]);
+            }
+        }
+        __syncwarp();
+        uint8_t *g0 = f.dst + (size_t)(2 * rp) * f.sd + (size_t)seg * kSegBytes;
+        uint8_t *g1 = g0 + f.sd;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const int off = (k * 32 + lane) * 16;
+            if (off < seg_bytes) {
+                st_stream_v4(g0 + off, *reinterpret_cast<const uint4 *>(t0 + off));
+                st_stream_v4(g1 + off, *reinterpret_cast<const uint4 *>(t1 + off));
+            }
+        }
+        if (RPT > 1) __syncwarp();                          // tile is re-used by the next row pair
+    }
+}
+
+// ================================================================================================
 // Persistent, TMA-pipelined kernel (the default).
 //
 // Item space: every frame contributes items (bulk/vector path: one item = 2 luma rows x 512 px;
