@@ -99,6 +99,26 @@ int vep_plan_launch_overlapped(vep_plan *plan, void *cuda_stream);
 int vep_plan_info(const vep_plan *plan, int *n_converted, int *n_ctas, int64_t *alg_bytes);
 void vep_plan_destroy(vep_plan *plan);
 
+/* No counterpart in the reference (it never touches a GPU): the same batched conversion for callers
+ * that are not allowed to allocate device memory — a process on a GPU slice or in a container whose
+ * memory was handed out in full at start-up, a plugin inside a host application whose own pool already
+ * owns almost all of HBM (a raw cudaMalloc can fail there although the pool has room), or a
+ * real-time loop that cannot take cudaMalloc's device-wide synchronisation mid-stream.  Needs no
+ * vep_ctx; works on the CURRENT device and on the caller's stream; calls no cudaMalloc/cudaFree or
+ * any other allocating routine.  Its descriptor tables live in a fixed array inside the library's
+ * CUDA module (about 532 KB on every GPU that loads the library, until the process exits), hence the
+ * limits: at most VEP_NOALLOC_MAX_FRAMES converted frames and VEP_NOALLOC_MAX_CTAS thread blocks per
+ * call (one block covers 8 x 512 px x 2 rows: a 1080p frame takes 270, 4K takes 1080); larger batches
+ * are refused with VEP_ERR_INVALID_ARG and the text says which limit — split them.
+ * The first call on each device also resolves the array's address on that device; make that first
+ * call before any stream capture is begun.  All calls share the one array per device and each call
+ * rewrites it: calls whose GPU work can overlap (different streams, different threads) race and
+ * must be serialised by the caller; calls queued on one stream are safe.  Outputs are byte-identical
+ * to vep_convert_batch. */
+#define VEP_NOALLOC_MAX_FRAMES 256
+#define VEP_NOALLOC_MAX_CTAS 65536
+int vep_convert_batch_noalloc(const vep_frame_desc *descs, int n, void *cuda_stream);
+
 /* ---- host pipeline: camera streams, pinned staging, tick (read_image.py:87-121) --------------
  * stream_open declares a camera (device_id in the reference) with a fixed decoded geometry.
  * `ring_depth` mirrors --memory_buffer / XADD MAXLEN (read_image.py:121): a result stays valid

@@ -9,12 +9,12 @@ libvepb200.so, hand-written sm_100a CUDA behind the C ABI of include/vepb200.h):
     assign_cameras                                                      (shard.py)
 """
 from ._abi import VepError, build_library  # noqa: F401
-from .frame_path import (FramePath, Plan, desc_from_device_ptrs, desc_from_tensors, make_meta,  # noqa: F401
-                         to_ndarray_bgr24, videoframe_framing)
+from .frame_path import (FramePath, Plan, convert_batch_noalloc, desc_from_device_ptrs, desc_from_tensors,  # noqa: F401
+                         make_meta, to_ndarray_bgr24, videoframe_framing)
 from .gate import CameraControl, DecodeGate, camera_active, poll_control  # noqa: F401
 from .producer import FrameProducer  # noqa: F401
 from .shard import assign_cameras  # noqa: F401
 
 __all__ = ["FramePath", "Plan", "make_meta", "videoframe_framing", "to_ndarray_bgr24", "DecodeGate",
            "CameraControl", "camera_active", "poll_control", "FrameProducer", "assign_cameras",
-           "VepError", "build_library", "desc_from_device_ptrs", "desc_from_tensors"]
+           "VepError", "build_library", "desc_from_device_ptrs", "desc_from_tensors", "convert_batch_noalloc"]

@@ -52,6 +52,7 @@ SIGNATURES = {
     "vep_create": (_i, [_i, _pp]),
     "vep_destroy": (None, [_p]),
     "vep_convert_batch": (_i, [_p, C.POINTER(FrameDesc), _i, _p]),
+    "vep_convert_batch_noalloc": (_i, [C.POINTER(FrameDesc), _i, _p]),
     "vep_plan_create": (_i, [_p, C.POINTER(FrameDesc), _i, _pp]),
     "vep_plan_launch": (_i, [_p, _p]),
     "vep_plan_launch_overlapped": (_i, [_p, _p]),

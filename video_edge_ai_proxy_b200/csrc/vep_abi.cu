@@ -854,3 +854,106 @@ extern "C" int vep_get_stats(vep_ctx *c, vep_stats *out) {
     *out = c->stats;
     return VEP_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// vep_convert_batch_noalloc — batched conversion for callers that must not allocate device memory.
+//
+// Who needs this: a producer that runs with a fixed device-memory budget and may not call
+// cudaMalloc once it is streaming — a GPU slice or container whose memory was handed out in full
+// at start-up, a host application (an inference server, a torch process) whose own pool already
+// holds nearly all of HBM so that a plugin's cudaMalloc can fail although the pool has room, or
+// a real-time loop that cannot afford cudaMalloc's device-wide synchronisation in the middle of
+// a tick.  The other entry points keep their descriptor tables in cudaMalloc'ed buffers (plans,
+// the per-context upload ring); this one keeps them in the fixed array below, which the CUDA
+// module carries itself.
+//
+// The kernel is the table-driven vep::yuv_to_bgr24_batched; only the home of its two tables
+// (FrameDev[], CtaWork[]) differs.
+// ------------------------------------------------------------------------------------------------
+static constexpr size_t kNoallocFramesBytes = (size_t)(VEP_NOALLOC_MAX_FRAMES + 1) * sizeof(FrameDev);
+static constexpr size_t kNoallocWorkOffset = (kNoallocFramesBytes + 255) / 256 * 256;
+static constexpr size_t kNoallocScratchBytes = kNoallocWorkOffset + (size_t)VEP_NOALLOC_MAX_CTAS * sizeof(CtaWork);
+
+// Device-resident scratch: one copy per GPU that loads this library, held until the process exits
+// (about 532 KB).  In HOST code this name is only a handle for cudaGetSymbolAddress — it is not a
+// device address and must never be handed to a kernel or a memcpy as one.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoallocScratchBytes];
+
+static std::mutex g_noalloc_mu;
+static void *g_noalloc_dev_ptr[64] = {};          // per device ordinal: address of g_noalloc_scratch on that GPU
+static FrameDev g_noalloc_h_frames[VEP_NOALLOC_MAX_FRAMES + 1];   // fixed host staging (no heap use on this path)
+static CtaWork g_noalloc_h_work[VEP_NOALLOC_MAX_CTAS];
+
+// Validation + table row for one descriptor; mirrors build_tables() without touching the heap.
+static int noalloc_frame(const vep_frame_desc &s, int i, FrameDev &f) {
+    if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_NV12) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
+    const int w = s.width, h = s.height;
+    if (w <= 0 || h <= 0 || w > kMaxDim || h > kMaxDim || (w & 1) || (h & 1))
+        return fail(VEP_ERR_GEOMETRY, "desc %d: %dx%d — 4:2:0 needs even, positive dimensions <= %d", i, w, h, kMaxDim);
+    const bool nv12 = s.fmt == VEP_FMT_NV12;
+    if (nv12 && h < 8) return fail(VEP_ERR_GEOMETRY, "desc %d: nv12 height %d < 8", i, h);
+    if (!s.plane[0] || !s.plane[1] || (!nv12 && !s.plane[2]) || !s.dst) return fail(VEP_ERR_INVALID_ARG, "desc %d: null plane or dst", i);
+    const int cw = nv12 ? w : w / 2;
+    if (s.stride[0] < w || s.stride[1] < cw || (!nv12 && s.stride[2] < cw) || s.dst_stride < 3 * w)
+        return fail(VEP_ERR_GEOMETRY, "desc %d: a stride is smaller than its row", i);
+    f = FrameDev{};
+    f.y = s.plane[0]; f.c0 = s.plane[1]; f.c1 = nv12 ? nullptr : s.plane[2]; f.dst = s.dst;
+    f.sy = s.stride[0]; f.sc0 = s.stride[1]; f.sc1 = nv12 ? 0 : s.stride[2]; f.sd = s.dst_stride;
+    f.w = w; f.h = h; f.fmt = s.fmt;
+    const size_t ca = nv12 ? 16 : 8;
+    const bool vec = (w % 16 == 0) && aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
+                     (nv12 || (aligned(f.c1, 8) && f.sc1 % 8 == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
+    f.fast = vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;   // the table-driven kernel knows these two paths
+    f.segs = (w + vep::kSegPx - 1) / vep::kSegPx;
+    return VEP_OK;
+}
+
+extern "C" int vep_convert_batch_noalloc(const vep_frame_desc *descs, int n, void *cuda_stream) {
+    if (n < 0 || (n > 0 && !descs)) return fail(VEP_ERR_INVALID_ARG, "descs is null or n < 0");
+    int dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(VEP_ERR_INVALID_ARG, "device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+
+    // ---- set-up, once per device, with that device current: resolve the scratch array's address there ----
+    if (!g_noalloc_dev_ptr[dev]) {
+        cudaDeviceProp prop;
+        CUDA_TRY(cudaGetDeviceProperties(&prop, dev));
+        if (prop.major < 10) return fail(VEP_ERR_CUDA, "device %d is sm_%d%d; this build carries sm_100a code only", dev, prop.major, prop.minor);
+        void *ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr) return fail(VEP_ERR_CUDA, "cudaGetSymbolAddress(scratch) on device %d -> %s", dev, cudaGetErrorString(e));
+        g_noalloc_dev_ptr[dev] = ptr;
+    }
+    uint8_t *scratch = static_cast<uint8_t *>(g_noalloc_dev_ptr[dev]);
+
+    // ---- tables into the fixed host staging, refusing anything beyond the stated maxima ----
+    int nf = 0, nw = 0;
+    for (int i = 0; i < n; ++i) {
+        if (!descs[i].convert) continue;
+        if (nf >= VEP_NOALLOC_MAX_FRAMES)
+            return fail(VEP_ERR_INVALID_ARG, "more than VEP_NOALLOC_MAX_FRAMES (%d) frames to convert in one call", VEP_NOALLOC_MAX_FRAMES);
+        FrameDev &f = g_noalloc_h_frames[nf];
+        int rc = noalloc_frame(descs[i], i, f);
+        if (rc) return rc;
+        const int units = f.fast != vep::PATH_GENERIC ? f.segs * (f.h / 2) : (f.w / 2) * (f.h / 2);
+        const int per_cta = f.fast != vep::PATH_GENERIC ? vep::kWarpsPerCta : vep::kGenericBlocksPerCta;
+        const int ctas = (units + per_cta - 1) / per_cta;
+        if (nw + ctas > VEP_NOALLOC_MAX_CTAS)
+            return fail(VEP_ERR_INVALID_ARG, "batch needs more than VEP_NOALLOC_MAX_CTAS (%d) thread blocks (about %d 1080p frames); split the call",
+                        VEP_NOALLOC_MAX_CTAS, VEP_NOALLOC_MAX_CTAS / 270);
+        for (int k = 0; k < ctas; ++k) g_noalloc_h_work[nw++] = CtaWork{nf, k * per_cta};
+        ++nf;
+    }
+    if (nf == 0) return VEP_OK;
+
+    // ---- both tables are rewritten in full for the entries this launch reads; nothing in the scratch has to
+    //      start at zero, and stale rows of an earlier, larger call are never indexed ----
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    CUDA_TRY(cudaMemcpyAsync(scratch, g_noalloc_h_frames, (size_t)nf * sizeof(FrameDev), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync(scratch + kNoallocWorkOffset, g_noalloc_h_work, (size_t)nw * sizeof(CtaWork), cudaMemcpyHostToDevice, st));
+    vep::yuv_to_bgr24_batched<0><<<nw, vep::kThreads, 0, st>>>(reinterpret_cast<const FrameDev *>(scratch),
+                                                               reinterpret_cast<const CtaWork *>(scratch + kNoallocWorkOffset));
+    CUDA_TRY(cudaGetLastError());
+    return VEP_OK;
+}

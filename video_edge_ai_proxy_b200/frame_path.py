@@ -274,3 +274,16 @@ def to_ndarray_bgr24(path: FramePath, fmt: str, planes: Sequence[np.ndarray]) ->
         return path.result(name).copy()
     finally:
         path.close_stream(name)
+
+
+def convert_batch_noalloc(descs: Sequence[FrameDesc], cuda_stream: int = 0):
+    """Batched conversion without any device allocation and without a FramePath (vep_convert_batch_noalloc).
+
+    For producers that may not allocate on the GPU while running: a fixed memory slice, a host
+    application that owns the allocator, a real-time loop.  The descriptor tables go into a fixed
+    array inside the library (limits: 256 frames / 65536 thread blocks per call, larger batches
+    raise VepError).  Runs on the current CUDA device and the given stream; calls that could overlap
+    on the GPU share that array and must be serialised by the caller.  The first call on a device
+    also does a one-time address lookup, so make it before starting a stream capture."""
+    arr = (FrameDesc * len(descs))(*descs)
+    check(_abi.lib().vep_convert_batch_noalloc(arr, len(descs), C.c_void_p(cuda_stream)), "vep_convert_batch_noalloc")
