@@ -259,6 +259,17 @@ def measured_peak():
         return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(kernel: str, workload: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+    ncu --set full capture of this same command (profiles/ncu_summary.json), or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_summary.json")) as f:
+            e = json.load(f)[f"{kernel}:{workload}"]
+        return e["dram_bytes_read"] + e["dram_bytes_write"]
+    except Exception:
+        return None
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -330,6 +341,20 @@ def run_gpu(args):
     achieved = plans[0].alg_bytes / (launch_ms / 1e3) / 1e9      # this rank's GPU (all ranks run the same plan)
     peak, peak_src = measured_peak()
 
+    # the same K ticks with every launch fully ordered after the previous one (what vep_plan_launch /
+    # vep_convert_batch do by default); reported beside the headline, not instead of it
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    torch.cuda.synchronize(dev)
+    s0.record(stream)
+    for i in range(args.steps):
+        plans[i % n_sets].launch(sptr, False)
+    s1.record(stream)
+    torch.cuda.synchronize(dev)
+    strict_ms = s0.elapsed_time(s1)
+    strict_ms = max_over_ranks(strict_ms) if world > 1 else strict_ms
+    strict_gbs = plans[0].alg_bytes / (strict_ms / args.steps / 1e3) / 1e9
+
     for p in plans:
         p.close()
     del outs, plans
@@ -386,8 +411,10 @@ def run_gpu(args):
                    "parallelism": f"cameras sharded {n}/GPU, no collective", "kernel": os.environ.get("VEP_KERNEL", "tick"),
                    "launch": "strict stream order" if args.strict_order else "vep_plan_launch_overlapped: consecutive ticks touch disjoint buffer sets"},
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                     "traffic": None, "peak_source": peak_src, "frac_of_nominal_8TBs": round(achieved / 8000.0, 4),
-                     "alg_bytes_per_launch": per_set_bytes, "kernel": {"persistent": "vep::yuv_to_bgr24_persistent", "oneshot": "vep::yuv_to_bgr24_batched"}.get(os.environ.get("VEP_KERNEL", "tick"), "vep::yuv_to_bgr24_tick")},
+                     "traffic": ncu_traffic(os.environ.get("VEP_KERNEL", "tick"), args.workload), "peak_source": peak_src, "frac_of_nominal_8TBs": round(achieved / 8000.0, 4),
+                     "alg_bytes_per_launch": per_set_bytes,
+                     "strict_stream_order": {"achieved": round(strict_gbs, 1), "frac": round(strict_gbs / peak, 4),
+                                             "frames_per_s": round(total_frames * args.steps / (strict_ms / 1e3), 1)}, "kernel": {"persistent": "vep::yuv_to_bgr24_persistent", "oneshot": "vep::yuv_to_bgr24_batched"}.get(os.environ.get("VEP_KERNEL", "tick"), "vep::yuv_to_bgr24_tick")},
         "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d_per_step), "d2h_bytes_per_step": int(d2h_per_step),
                 "steps": e2e_steps, "api": "FramePath.submit (host planes -> pinned staging) + tick_begin/tick_wait (3 ticks in flight) + result_packed",
                 "pcie_gbs": round((h2d_per_step + d2h_per_step) * e2e_steps / e2e_s / 1e9, 2), "message_bytes": msg_bytes},
@@ -424,7 +451,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="16x1080p", choices=sorted(WORKLOADS))
     ap.add_argument("--sets", type=int, default=9, help="minimum number of rotating buffer sets")
-    ap.add_argument("--e2e-steps", type=int, default=60)
+    ap.add_argument("--e2e-steps", type=int, default=300)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--strict-order", action="store_true", help="launch every tick fully ordered after the previous one (no overlap)")
     args = ap.parse_args()

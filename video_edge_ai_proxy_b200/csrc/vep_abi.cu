@@ -239,6 +239,9 @@ static void fill_tick(const Tables &t, std::vector<uint8_t> &blob) {
     const int n = t.n_converted;
     P->n_frames = n;
     P->wait_prior = 1;
+    int per = n ? t.tick_cta_begin[1] - t.tick_cta_begin[0] : 0;
+    for (int i = 1; i < n && per > 0; ++i) if (t.tick_cta_begin[i + 1] - t.tick_cta_begin[i] != per) per = 0;
+    P->uniform_ctas = (n > 0 && n <= 65535) ? per : 0;
     for (int i = 0; i <= n; ++i) P->cta_begin[i] = t.tick_cta_begin[i];
     for (int i = 0; i < n; ++i) P->frames[i] = t.frames[i];
 }
@@ -262,7 +265,8 @@ static int launch_tick(const vep_ctx *c, int cap, const std::vector<uint8_t> &bl
     const void *fn = cap == kTickCapSmall ? tick_kernel<kTickCapSmall>(c->rpt, c->minb) : tick_kernel<kTickCapLarge>(c->rpt, c->minb);
     void *args[1] = {const_cast<uint8_t *>(blob.data())};
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(grid);
+    const int32_t *hdr = reinterpret_cast<const int32_t *>(blob.data());   // n_frames, wait_prior, uniform_ctas
+    cfg.gridDim = hdr[2] > 0 ? dim3(hdr[2], hdr[0]) : dim3(grid);
     cfg.blockDim = dim3(vep::kThreads);
     cfg.stream = st;
     cudaLaunchAttribute attr[1];

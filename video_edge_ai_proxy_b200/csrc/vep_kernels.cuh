@@ -370,7 +370,9 @@ struct TickParams {
     int32_t n_frames;
     int32_t wait_prior;      // 1: griddepcontrol.wait before touching memory (ordinary stream order);
                              // 0: the caller declared this launch independent of the previous kernel
-    int32_t pad_[2];
+    int32_t uniform_ctas;    // > 0: every frame has this many CTAs and the grid is (uniform_ctas, n_frames):
+                             //      blockIdx.y is the frame, no search (homogeneous camera fleets)
+    int32_t pad_;
     int32_t cta_begin[(NF + 1 + 3) / 4 * 4];   // cta_begin[f] = first CTA of frame f; [n_frames] = grid size
     FrameDev frames[NF];
 };
@@ -384,12 +386,11 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     // vouched for independence, wait here until the previous kernel's writes are complete.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (p.wait_prior) asm volatile("griddepcontrol.wait;" ::: "memory");
-    const int cta = blockIdx.x;
-    int fi = 0;
-    if (NF <= 16) {
-#pragma unroll
-        for (int i = 1; i < NF; ++i) fi += (i < p.n_frames && cta >= p.cta_begin[i]) ? 1 : 0;   // independent constant reads
-    } else {
+    int cta = blockIdx.x, fi = 0;
+    if (p.uniform_ctas > 0) {
+        fi = blockIdx.y;
+        cta += p.cta_begin[fi];
+    } else {   // mixed fleet: binary search over the CTA prefix in the constant bank (uniform datapath)
         int lo = 0, hi = p.n_frames - 1;
         while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (cta >= p.cta_begin[mid]) lo = mid; else hi = mid - 1; }
         fi = lo;
