@@ -42,10 +42,13 @@ WORKLOADS = {
     # name: (cameras per GPU, fmt, w, h, description)
     "16x1080p": (16, "yuv420p", 1920, 1080, "16 synthetic 1080p yuv420p cameras per GPU, one batched launch per tick (BASELINE configs[1])"),
     "8x1080p": (8, "yuv420p", 1920, 1080, "8 synthetic 1080p yuv420p cameras per GPU (BASELINE configs[2] layout: 64 cameras over 8 GPUs)"),
-    "8x4k-nv12": (8, "nv12", 3840, 2160, "8 synthetic 3840x2160 NV12 cameras per GPU (BASELINE configs[3] frames)"),
+    "8x4k-nv12": (8, "nv12", 3840, 2160, "8 synthetic 3840x2160 NV12 cameras per GPU, every frame converted"),
+    "8x4k-nv12-keyframe": (8, "nv12", 3840, 2160, "8 synthetic 3840x2160 NV12 cameras per GPU, key-frame-only: GOP 30, staggered phases, only key frames are converted (BASELINE configs[3])"),
+    "mixed128-skip": (128, "yuv420p", 0, 0, "128-camera fleet per GPU: 43 x 640x480, 43 x 1280x720, 42 x 1920x1080 yuv420p, interval-skip: each camera converts a frame with p = 0.25 per tick (seeded Bernoulli, seed = tick) (BASELINE configs[4])"),
     "64x1080p": (64, "yuv420p", 1920, 1080, "64 synthetic 1080p yuv420p cameras on one GPU (launch-overhead study, not a BASELINE config)"),
     "1x480p": (1, "yuv420p", 640, 480, "one 640x480 yuv420p stream (BASELINE configs[0])"),
 }
+MIXED_SIZES = [(640, 480)] * 43 + [(1280, 720)] * 43 + [(1920, 1080)] * 42
 
 
 # ------------------------------------------------------------------------------------------------
@@ -58,7 +61,20 @@ def dist_env():
 def cameras_for_rank(workload: str, rank: int, world: int):
     """Static partition: rank r owns cameras [r*n, (r+1)*n) — disjoint sets, no exchange step."""
     n, fmt, w, h, _ = WORKLOADS[workload]
+    if workload == "mixed128-skip":
+        return [dict(camera=rank * n + i, fmt=fmt, w=MIXED_SIZES[i][0], h=MIXED_SIZES[i][1], seed=rank * n + i) for i in range(n)]
     return [dict(camera=rank * n + i, fmt=fmt, w=w, h=h, seed=rank * n + i) for i in range(n)]
+
+
+def schedule_for(workload: str, n_cams: int):
+    """The repeating tick pattern: for each tick of the cycle, the local camera indices whose frame is
+    converted (the decode gate's decision; every camera is OFFERED one frame per tick)."""
+    if workload == "8x4k-nv12-keyframe":       # GOP 30, camera c's key frames at ticks = phase_c (mod 30)
+        phase = [(c * 30) // n_cams for c in range(n_cams)]
+        return [[c for c in range(n_cams) if phase[c] == t] for t in range(30)]
+    if workload == "mixed128-skip":            # 16 distinct ticks, selection seeded by the tick index
+        return [[int(c) for c in np.nonzero(np.random.default_rng(t).random(n_cams) < 0.25)[0]] for t in range(16)]
+    return [list(range(n_cams))]
 
 
 def _reduce(value: float, op, device: str):
@@ -168,9 +184,10 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # CPU arm: the reference's own path on host cores (libswscale via the oracle binding)
 # ------------------------------------------------------------------------------------------------
-def cpu_frames_per_sec(cams, steps: int, warmup: int, threads: int, with_tobytes: bool = True):
-    """Each step converts one frame of every camera (the same tick the GPU arm converts), spread
-    over `threads` host threads; ctypes releases the GIL inside sws_scale.  Returns (fps, seconds)."""
+def cpu_frames_per_sec(cams, steps: int, warmup: int, threads: int, with_tobytes: bool = True, sched=None):
+    """Each step converts the frames the tick's schedule selects (default: one frame of every camera —
+    the same tick the GPU arm converts), spread over `threads` host threads; ctypes releases the GIL
+    inside sws_scale.  Returns (converted frames per second, seconds)."""
     from oracle import swscale_live as live   # bench.py's CPU leg is allowed to execute oracle/
     from video_edge_ai_proxy_b200.synth import make_planes
     if not live.available():
@@ -188,16 +205,20 @@ def cpu_frames_per_sec(cams, steps: int, warmup: int, threads: int, with_tobytes
             return cv.result().nbytes                # one H*W*3 copy = np.ndarray.tobytes(img)  :97
         return 0
 
+    sched = sched or [list(range(len(cams)))]
+    done = 0
     with ThreadPoolExecutor(threads) as pool:
-        for _ in range(warmup):
-            list(pool.map(one, convs))
+        for i in range(warmup):
+            list(pool.map(one, [convs[c] for c in sched[i % len(sched)]]))
         t0 = time.perf_counter()
-        for _ in range(steps):
-            list(pool.map(one, convs))
+        for i in range(steps):
+            sel = sched[i % len(sched)]
+            list(pool.map(one, [convs[c] for c in sel]))
+            done += len(sel)
         dt = time.perf_counter() - t0
     for cv in convs:
         cv.close()
-    return steps * len(cams) / dt, dt
+    return done / dt, dt
 
 
 def host_threads():
@@ -222,22 +243,27 @@ def run_reference(args):
     if rank != 0:
         return 0
     n, fmt, w, h, desc = WORKLOADS[args.workload]
-    cams = cameras_for_rank(args.workload, 0, 1)
+    # the whole job's cameras (weak scaling: n per GPU); the reference runs one worker per camera
+    # (rtsp_process_manager.go:106-111), so it can use min(host threads, cameras) cores
+    G = max(args.gpus, 1)
+    cams = [c for r in range(G) for c in cameras_for_rank(args.workload, r, G)]
+    local = schedule_for(args.workload, n)                 # every rank runs the same pattern on its own cameras
+    sched = [[r * n + c for r in range(G) for c in pat] for pat in local]
     T = host_threads()
     try:
-        fps, dt = cpu_frames_per_sec(cams, args.steps, args.warmup, T, with_tobytes=True)
+        fps, dt = cpu_frames_per_sec(cams, args.steps, args.warmup, T, with_tobytes=True, sched=sched)
     except Exception as e:
         print(json.dumps({"impl": "reference", "unavailable": str(e)[:200]}))
         return 0
     used = min(T, len(cams))
     line = {
-        "impl": "reference", "metric": METRIC, "value": round(fps, 2), "unit": UNIT, "n_gpus": args.gpus,
+        "impl": "reference", "metric": METRIC if (w, h) == (1920, 1080) else "bgr24_frames_per_sec", "value": round(fps, 2), "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 4),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {desc}", "frames_per_step": len(cams),
                    "cpu": cpu_model(), "note": "host cores only; the reference has no GPU path"},
         "cpu_baseline": {"value": round(fps, 2), "unit": UNIT, "cores": used, "kind": "reference",
-                         "sample": f"{args.steps} ticks x {len(cams)} frames {w}x{h} {fmt}: libswscale 9.1.100 sws_scale "
+                         "sample": f"{args.steps} ticks of the workload ({len(cams)} cameras, {fmt}, frames selected per tick as in the GPU arm): libswscale 9.1.100 sws_scale "
                                    f"(SWS_BILINEAR, the call PyAV makes for read_image.py:94) + tobytes (:97), "
                                    f"{used} threads of {T} available"},
         "e2e": {"value": round(fps, 2), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -286,10 +312,14 @@ def run_gpu(args):
 
     n, fmt, w, h, desc = WORKLOADS[args.workload]
     cams = cameras_for_rank(args.workload, rank, world)
-    frame_alg_bytes = int(ALG_BYTES_PER_PX * w * h)
-    per_set_bytes = n * frame_alg_bytes
+    sched = schedule_for(args.workload, len(cams))
+    alg = [int(ALG_BYTES_PER_PX * c["w"] * c["h"]) for c in cams]
+    per_set_bytes = sum(alg)
     l2_bytes = torch.cuda.get_device_properties(dev).L2_cache_size
     n_sets = max(args.sets, 2, -(-3 * l2_bytes // per_set_bytes))   # footprint of the rotation >= 3x L2
+    import math
+    while math.gcd(n_sets, len(sched)) != 1:
+        n_sets += 1                                                   # coprime: every pattern meets every buffer set
 
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -297,28 +327,45 @@ def run_gpu(args):
 
     # ---- resident inputs: n_sets copies of every camera's planes, separate outputs per set ----------
     host_planes = [make_planes(c["fmt"], c["w"], c["h"], c["seed"]) for c in cams]
-    plans, outs = [], []
+    plans, outs = [], []          # plans[s][p]: buffer set s, tick pattern p (None when the pattern converts nothing)
     for s in range(n_sets):
         descs, set_outs = [], []
         for c, hp in zip(cams, host_planes):
             planes = [torch.from_numpy(p).to(dev) for p in hp]
-            out = torch.empty((c["h"], c["w"], 3), dtype=torch.uint8, device=dev)
+            out = torch.zeros((c["h"], c["w"], 3), dtype=torch.uint8, device=dev)
             descs.append(desc_from_tensors(c["fmt"], planes, out))
             set_outs.append((planes, out))
-        plans.append(path.plan(descs))
+        row = []
+        for pat in sched:
+            row.append(path.plan([descs[c] for c in pat]) if pat else None)
+        plans.append(row)
         outs.append(set_outs)
     stream = torch.cuda.current_stream(dev)
     sptr = stream.cuda_stream
+    n_pat = len(sched)
 
-    for i in range(max(args.warmup, 3, n_sets)):      # every buffer set is converted at least once
-        plans[i % n_sets].launch(sptr)
+    def run_ticks(first, count, overlapped):
+        launches = 0
+        for i in range(first, first + count):
+            pl = plans[i % n_sets][i % n_pat]
+            if pl is not None:
+                pl.launch(sptr, overlapped)
+                launches += 1
+        return launches
+
+    warm = max(args.warmup, 3, n_sets * n_pat)        # every (set, pattern) pair is converted at least once
+    run_ticks(0, warm, False)
     torch.cuda.synchronize(dev)
     # every set must hold the same, non-trivial result (same inputs): the kernel really ran everywhere
-    ref_sum = [int(o.sum(dtype=torch.int64).item()) for _, o in outs[0]]
+    touched = sorted({c for pat in sched for c in pat})
+    ref_sum = [int(outs[0][c][1].sum(dtype=torch.int64).item()) for c in touched]
     for s in range(1, n_sets):
-        got = [int(o.sum(dtype=torch.int64).item()) for _, o in outs[s]]
+        got = [int(outs[s][c][1].sum(dtype=torch.int64).item()) for c in touched]
         if got != ref_sum or min(got) == 0:
             raise SystemExit(f"bench.py: buffer set {s} disagrees with set 0 — refusing to time a broken kernel")
+
+    conv_in = lambda first, count: sum(len(sched[i % n_pat]) for i in range(first, first + count))
+    bytes_in = lambda first, count: sum(alg[c] for i in range(first, first + count) for c in sched[i % n_pat])
 
     # ---- value: K steps, device-timed on the launching stream ---------------------------------------
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -327,18 +374,20 @@ def run_gpu(args):
     w0 = time.perf_counter()
     e0.record(stream)
     overlapped = not args.strict_order     # consecutive ticks use disjoint buffer sets -> may overlap
-    for i in range(args.steps):
-        plans[i % n_sets].launch(sptr, overlapped)
+    gpu_launches = run_ticks(warm, args.steps, overlapped)
     e1.record(stream)
     torch.cuda.synchronize(dev)
     w1 = time.perf_counter()
     barrier()
     dev_ms = e0.elapsed_time(e1)
     dev_ms = max_over_ranks(dev_ms) if world > 1 else dev_ms
-    total_frames = sum_over_ranks(n) if world > 1 else n
-    value = total_frames * args.steps / (dev_ms / 1e3)
+    converted = conv_in(warm, args.steps)
+    total_frames = sum_over_ranks(converted) if world > 1 else converted          # whole job, K steps
+    offered_frames = (sum_over_ranks(len(cams)) if world > 1 else len(cams)) * args.steps
+    value = total_frames / (dev_ms / 1e3)
     launch_ms = dev_ms / args.steps
-    achieved = plans[0].alg_bytes / (launch_ms / 1e3) / 1e9      # this rank's GPU (all ranks run the same plan)
+    timed_bytes = bytes_in(warm, args.steps)
+    achieved = timed_bytes / (dev_ms / 1e3) / 1e9      # this rank's GPU (all ranks run the same schedule)
     peak, peak_src = measured_peak()
 
     # the same K ticks with every launch fully ordered after the previous one (what vep_plan_launch /
@@ -347,16 +396,18 @@ def run_gpu(args):
     barrier()
     torch.cuda.synchronize(dev)
     s0.record(stream)
-    for i in range(args.steps):
-        plans[i % n_sets].launch(sptr, False)
+    run_ticks(warm, args.steps, False)
     s1.record(stream)
     torch.cuda.synchronize(dev)
     strict_ms = s0.elapsed_time(s1)
     strict_ms = max_over_ranks(strict_ms) if world > 1 else strict_ms
-    strict_gbs = plans[0].alg_bytes / (strict_ms / args.steps / 1e3) / 1e9
+    strict_gbs = timed_bytes / (strict_ms / 1e3) / 1e9
 
-    for p in plans:
-        p.close()
+    for row in plans:
+        for p in row:
+            if p is not None:
+                p.close()
+    plans = []
     del outs, plans
     torch.cuda.empty_cache()
 
@@ -368,70 +419,76 @@ def run_gpu(args):
     meta = make_meta(timestamp=1604660000123, pts=900000, dts=897000, time_base=1 / 90000, is_keyframe=True, frame_type="I", keyframe=1)
     pool = ThreadPoolExecutor(min(len(cams), host_threads()))
 
-    def submit_all():
-        list(pool.map(lambda a: path.submit(a[0], a[1], meta), zip(names, host_planes)))
+    def submit_all(tick):
+        sel = set(sched[tick % n_pat])
+        list(pool.map(lambda a: path.submit(a[1], a[2], meta, convert=a[0] in sel), zip(range(len(names)), names, host_planes)))
+        return sorted(sel)
 
-    def consume():
+    def consume(sel):
         tot = 0
-        for name in names:
-            tot += len(path.result_packed(name))      # the message a producer hands to XADD
+        for c in sel:
+            tot += len(path.result_packed(names[c]))      # the message a producer hands to XADD
         return tot
 
-    for _ in range(3):
-        submit_all(); path.tick(); consume()
+    for t in range(3):
+        consume_sel = submit_all(t); path.tick(); consume(consume_sel)
     barrier()
     torch.cuda.synchronize(dev)
+    base_stats = path.stats()
     x0 = time.perf_counter()
-    depth, waiting = 3, 0                             # ticks in flight: staging copy + H2D of later ticks
+    depth, pending, msg_bytes = 3, [], 0              # ticks in flight: staging copy + H2D of later ticks
     for i in range(e2e_steps):                        # overlap the D2H of earlier ones (PCIe is full duplex)
-        submit_all(); path.tick_begin(); waiting += 1
-        if waiting == depth:
-            path.tick_wait(); msg_bytes = consume(); waiting -= 1
-    while waiting:
-        path.tick_wait(); msg_bytes = consume(); waiting -= 1
+        pending.append(submit_all(i)); path.tick_begin()
+        if len(pending) == depth:
+            path.tick_wait(); msg_bytes = consume(pending.pop(0)) or msg_bytes
+    while pending:
+        path.tick_wait(); msg_bytes = consume(pending.pop(0)) or msg_bytes
     torch.cuda.synchronize(dev)
     x1 = time.perf_counter()
     barrier()
     e2e_s = max_over_ranks(x1 - x0) if world > 1 else (x1 - x0)
-    e2e_value = total_frames * e2e_steps / e2e_s
+    e2e_conv = conv_in(0, e2e_steps)
+    e2e_value = (sum_over_ranks(e2e_conv) if world > 1 else e2e_conv) / e2e_s
     st = path.stats()
-    h2d_per_step = st["h2d_bytes"] // max(st["ticks"], 1)
-    d2h_per_step = st["d2h_bytes"] // max(st["ticks"], 1)
+    h2d_per_step = (st["h2d_bytes"] - base_stats["h2d_bytes"]) // e2e_steps
+    d2h_per_step = (st["d2h_bytes"] - base_stats["d2h_bytes"]) // e2e_steps
     pool.shutdown()
     sampler.stop()
     clocks = sampler.summary([(w0, w1), (x0, x1)])
     path.close()
 
     line = {
-        "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "metric": METRIC if (w, h) == (1920, 1080) else "bgr24_frames_per_sec", "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": round(launch_ms, 5), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {desc}", "frames_per_step_per_gpu": n, "format": fmt, "width": w, "height": h,
+        "config": {"workload": f"{args.workload}: {desc}", "cameras_per_gpu": len(cams), "converted_frames_per_step_per_gpu": round(converted / args.steps, 3),
+                   "offered_frames_per_s": round(offered_frames / (dev_ms / 1e3), 1), "format": fmt,
                    "l2": f"inputs/outputs rotate over {n_sets} buffer sets of {per_set_bytes / 1e6:.0f} MB (> {l2_bytes / 1e6:.0f} MB L2)",
                    "parallelism": f"cameras sharded {n}/GPU, no collective", "kernel": os.environ.get("VEP_KERNEL", "tick"),
                    "launch": "strict stream order" if args.strict_order else "vep_plan_launch_overlapped: consecutive ticks touch disjoint buffer sets"},
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
                      "traffic": ncu_traffic(os.environ.get("VEP_KERNEL", "tick"), args.workload), "peak_source": peak_src, "frac_of_nominal_8TBs": round(achieved / 8000.0, 4),
-                     "alg_bytes_per_launch": per_set_bytes,
+                     "alg_bytes_per_launch": int(timed_bytes / max(gpu_launches, 1)),
                      "strict_stream_order": {"achieved": round(strict_gbs, 1), "frac": round(strict_gbs / peak, 4),
-                                             "frames_per_s": round(total_frames * args.steps / (strict_ms / 1e3), 1)}, "kernel": {"persistent": "vep::yuv_to_bgr24_persistent", "oneshot": "vep::yuv_to_bgr24_batched"}.get(os.environ.get("VEP_KERNEL", "tick"), "vep::yuv_to_bgr24_tick")},
+                                             "frames_per_s": round(total_frames / (strict_ms / 1e3), 1)}, "kernel": {"persistent": "vep::yuv_to_bgr24_persistent", "oneshot": "vep::yuv_to_bgr24_batched"}.get(os.environ.get("VEP_KERNEL", "tick"), "vep::yuv_to_bgr24_tick")},
         "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d_per_step), "d2h_bytes_per_step": int(d2h_per_step),
                 "steps": e2e_steps, "api": "FramePath.submit (host planes -> pinned staging) + tick_begin/tick_wait (3 ticks in flight) + result_packed",
                 "pcie_gbs": round((h2d_per_step + d2h_per_step) * e2e_steps / e2e_s / 1e9, 2), "message_bytes": msg_bytes},
-        "gpu_launches": args.steps,
+        "gpu_launches": gpu_launches,
         "clocks": clocks,
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         T = host_threads()
         try:
             # bounded sample: ~20 s of CPU work in total, spread over the host threads
-            est_ms = 1.6 * (w * h) / (1920 * 1080)
-            cpu_steps = max(3, int(20000 / (est_ms * n)))
-            fps, dt = cpu_frames_per_sec(cams, cpu_steps, 2, T, with_tobytes=True)
-            fps_scale, _ = cpu_frames_per_sec(cams, max(3, cpu_steps // 4), 1, T, with_tobytes=False)
+            frac = converted / max(args.steps * len(cams), 1)                                         # share of frames the gate lets through
+            est_ms = 1.6 * (per_set_bytes / 4.5) / (1920 * 1080) * (5.0 if fmt == "nv12" else 1.0) * max(frac, 0.01)
+            cpu_steps = max(3, int(20000 / est_ms))
+            fps, dt = cpu_frames_per_sec(cams, cpu_steps, 2, T, with_tobytes=True, sched=sched if n_pat > 1 else None)
+            fps_scale, _ = cpu_frames_per_sec(cams, max(3, cpu_steps // 4), 1, T, with_tobytes=False, sched=sched if n_pat > 1 else None)
             used = min(T, len(cams))
             line["cpu_baseline"] = {"value": round(fps, 1), "unit": UNIT, "cores": used, "kind": "reference",
-                                    "sample": f"{cpu_steps} ticks x {n} frames {w}x{h} {fmt} ({dt:.1f} s wall): libswscale 9.1.100 sws_scale "
+                                    "sample": f"{cpu_steps} ticks x {n} frames of the workload ({fmt}, frames selected per tick as in the GPU arm) ({dt:.1f} s wall): libswscale 9.1.100 sws_scale "
                                               f"(what PyAV calls for read_image.py:94) + tobytes (:97) on {used} threads of {T}; "
                                               f"sws_scale alone: {fps_scale:.0f} frames/s; cpu: {cpu_model()}"}
         except Exception as e:
