@@ -39,7 +39,10 @@ typedef enum {
 typedef enum {
     VEP_FMT_YUV420P = 0,   /* planar, limited (MPEG) range  — swscale coefficient set 1 */
     VEP_FMT_YUVJ420P = 1,  /* planar, full (JPEG) range     — swscale coefficient set 2 */
-    VEP_FMT_NV12 = 2       /* Y plane + interleaved UV, limited range */
+    VEP_FMT_NV12 = 2,      /* Y plane + interleaved UV, limited range */
+    VEP_FMT_NV21 = 3,      /* as NV12 with V first in each chroma pair */
+    VEP_FMT_YUV422P = 4,   /* planar 4:2:2, limited range: chroma planes are (W/2) x H */
+    VEP_FMT_YUVJ422P = 5   /* planar 4:2:2, full range (what MJPEG cameras decode to) */
 } vep_pixfmt;
 
 /* One frame of a batched conversion, all pointers in DEVICE memory.
@@ -47,11 +50,11 @@ typedef enum {
  * plane[]/stride[] are the AVFrame planes and linesizes, dst is the (H, W, 3) uint8 result
  * (dst_stride = 3*width for the contiguous array PyAV returns after its padding strip). */
 typedef struct {
-    const uint8_t *plane[3]; /* Y,U,V  (nv12: Y,UV,NULL) */
+    const uint8_t *plane[3]; /* Y,U,V  (nv12/nv21: Y,UV,NULL) */
     int32_t stride[3];       /* bytes per row of each plane */
     uint8_t *dst;            /* B,G,R interleaved */
     int32_t dst_stride;      /* bytes per output row, >= 3*width */
-    int32_t width, height;   /* both even; nv12 needs height >= 8 */
+    int32_t width, height;   /* both even; nv12/nv21 need height >= 8 */
     int32_t fmt;             /* vep_pixfmt */
     int32_t convert;         /* 0: the decode gate skipped this frame (read_image.py:80), no work */
 } vep_frame_desc;

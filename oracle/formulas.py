@@ -190,7 +190,31 @@ def nv12_to_bgr24(Y, UV) -> np.ndarray:
     return out
 
 
+def yuv422p_to_bgr24(Y, U, V, full_range: bool = False) -> np.ndarray:
+    """4:2:2 planar (MJPEG cameras decode to yuvj422p).  Probed against the live library: libswscale keeps
+    every chroma row — luma row j uses chroma row j, horizontally nearest — and feeds the same SIMD
+    output stage as formula A (all rows, including the last two).  U/V are (H, W/2)."""
+    h, w = Y.shape
+    k = coeffs_simd(full_range)
+    rep = lambda a: np.repeat(a, 2, axis=1)[:, :w]
+    return _simd_output_stage(Y, (rep(U).astype(np.int32) << 3) - 1024, (rep(V).astype(np.int32) << 3) - 1024, k)
+
+
+def nv21_to_bgr24(Y, VU) -> np.ndarray:
+    """NV21 = NV12 with V first in each chroma pair; identical arithmetic (probed)."""
+    UV = np.empty_like(VU)
+    UV[:, 0::2] = VU[:, 1::2]
+    UV[:, 1::2] = VU[:, 0::2]
+    return nv12_to_bgr24(Y, UV)
+
+
 def to_bgr24(fmt: str, planes) -> np.ndarray:
+    if fmt == "yuv422p":
+        return yuv422p_to_bgr24(planes[0], planes[1], planes[2], False)
+    if fmt == "yuvj422p":
+        return yuv422p_to_bgr24(planes[0], planes[1], planes[2], True)
+    if fmt == "nv21":
+        return nv21_to_bgr24(planes[0], planes[1])
     if fmt == "yuv420p":
         return yuv420p_to_bgr24(planes[0], planes[1], planes[2], False)
     if fmt == "yuvj420p":

@@ -30,7 +30,8 @@ def _load():
         _lib = ctypes.CDLL(_SO)
         p, i = ctypes.c_void_p, ctypes.c_int
         _lib.port_yuv420p_to_bgr24.argtypes = [p, i, p, i, p, i, i, i, i, p, i]
-        _lib.port_nv12_to_bgr24.argtypes = [p, i, p, i, i, i, p, i]
+        _lib.port_yuv422p_to_bgr24.argtypes = [p, i, p, i, p, i, i, i, i, p, i]
+        _lib.port_nv12_to_bgr24.argtypes = [p, i, p, i, i, i, p, i, i]
     return _lib
 
 
@@ -44,10 +45,15 @@ def to_bgr24(fmt: str, planes) -> np.ndarray:
         r = lib.port_yuv420p_to_bgr24(Y.ctypes.data, Y.strides[0], U.ctypes.data, U.strides[0],
                                       V.ctypes.data, V.strides[0], w, h,
                                       1 if fmt == "yuvj420p" else 0, out.ctypes.data, w * 3)
-    elif fmt == "nv12":
+    elif fmt in ("yuv422p", "yuvj422p"):
+        Y, U, V = planes
+        r = lib.port_yuv422p_to_bgr24(Y.ctypes.data, Y.strides[0], U.ctypes.data, U.strides[0],
+                                      V.ctypes.data, V.strides[0], w, h,
+                                      1 if fmt == "yuvj422p" else 0, out.ctypes.data, w * 3)
+    elif fmt in ("nv12", "nv21"):
         Y, UV = planes
         r = lib.port_nv12_to_bgr24(Y.ctypes.data, Y.strides[0], UV.ctypes.data, UV.strides[0],
-                                   w, h, out.ctypes.data, w * 3)
+                                   w, h, out.ctypes.data, w * 3, 1 if fmt == "nv21" else 0)
     else:
         raise ValueError(fmt)
     if r != 0:

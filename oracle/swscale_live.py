@@ -23,7 +23,7 @@ import threading
 import numpy as np
 
 # AVPixelFormat ids of the bundled FFmpeg (checked in `_load()` via av_get_pix_fmt).
-PIX_FMT = {"yuv420p": 0, "bgr24": 3, "yuvj420p": 12, "nv12": 23}
+PIX_FMT = {"yuv420p": 0, "bgr24": 3, "yuv422p": 4, "yuvj420p": 12, "yuvj422p": 13, "nv12": 23, "nv21": 24}
 SWS_BILINEAR = 2  # PyAV's default `interpolation` for VideoFrame.reformat
 
 # swscale's SIMD row loops run in 16/32-pixel steps and touch bytes past the visible row end
@@ -135,12 +135,13 @@ class Converter:
         if not self.ctx:
             raise RuntimeError("sws_getContext failed")
         self.y, self.sy, self._ky = _padded(h, w)
-        if fmt == "nv12":
+        ch = h if fmt in ("yuv422p", "yuvj422p") else h // 2
+        if fmt in ("nv12", "nv21"):
             self.c0, self.s0, self._k0 = _padded(h // 2, w)
             self.c1 = None
         else:
-            self.c0, self.s0, self._k0 = _padded(h // 2, w // 2)
-            self.c1, self.s1, self._k1 = _padded(h // 2, w // 2)
+            self.c0, self.s0, self._k0 = _padded(ch, w // 2)
+            self.c1, self.s1, self._k1 = _padded(ch, w // 2)
         self.dst, self.sd, self._kd = _padded(h, w * 3)
         self._src = (ctypes.c_void_p * 4)(self.y.ctypes.data, self.c0.ctypes.data,
                                           self.c1.ctypes.data if self.c1 is not None else None,
@@ -153,7 +154,7 @@ class Converter:
     def load(self, planes):
         w, h = self.w, self.h
         self.y[:, :w] = planes[0]
-        if self.fmt == "nv12":
+        if self.fmt in ("nv12", "nv21"):
             self.c0[:, :w] = planes[1]
         else:
             self.c0[:, :w // 2] = planes[1]

@@ -72,13 +72,29 @@ int port_yuv420p_to_bgr24(const uint8_t *Y, int sy, const uint8_t *U, int su, co
     return 0;
 }
 
-/* Formula C (limited range).  H >= 8. */
+/* 4:2:2 planar: luma row j uses chroma row j (oracle/formulas.py: yuv422p_to_bgr24). */
+int port_yuv422p_to_bgr24(const uint8_t *Y, int sy, const uint8_t *U, int su, const uint8_t *V,
+                          int sv, int w, int h, int full_range, uint8_t *dst, int sd)
+{
+    if (w <= 0 || h <= 0 || (w & 1) || (h & 1) || w > MAXW) return -1;
+    const simd_k *k = full_range ? &K_FULL : &K_LIMITED;
+    int Uw[MAXW / 2], Vw[MAXW / 2];
+    for (int j = 0; j < h; j++) {
+        const uint8_t *u = U + (size_t)j * su, *v = V + (size_t)j * sv;
+        for (int i = 0; i < w / 2; i++) { Uw[i] = (u[i] << 3) - 1024; Vw[i] = (v[i] << 3) - 1024; }
+        row_simd(Y + (size_t)j * sy, Uw, Vw, dst + (size_t)j * sd, w, k);
+    }
+    return 0;
+}
+
+/* Formula C (limited range).  H >= 8.  vu != 0: NV21 byte order (V first). */
 int port_nv12_to_bgr24(const uint8_t *Y, int sy, const uint8_t *UV, int suv, int w, int h,
-                       uint8_t *dst, int sd)
+                       uint8_t *dst, int sd, int vu)
 {
     if (w <= 0 || h < 8 || (w & 1) || (h & 1) || w > MAXW) return -1;
     int a0[MAXW / 2], a1[MAXW / 2];
     const int hc = h / 2;
+    const int iu = vu ? 1 : 0, iv = vu ? 0 : 1;
     for (int j = 0; j < h; j++) {
         const int k = j >> 1;
         const uint8_t *y = Y + (size_t)j * sy;
@@ -88,11 +104,11 @@ int port_nv12_to_bgr24(const uint8_t *Y, int sy, const uint8_t *UV, int suv, int
             const uint8_t *up = UV + (size_t)(k > 0 ? k - 1 : 0) * suv;
             for (int i = 0; i < w / 2; i++) {
                 if (j & 1) {
-                    a0[i] = (cur[2 * i] << 3) - 1024;
-                    a1[i] = (cur[2 * i + 1] << 3) - 1024;
+                    a0[i] = (cur[2 * i + iu] << 3) - 1024;
+                    a1[i] = (cur[2 * i + iv] << 3) - 1024;
                 } else {
-                    a0[i] = ((up[2 * i] + cur[2 * i]) << 2) - 1024;
-                    a1[i] = ((up[2 * i + 1] + cur[2 * i + 1]) << 2) - 1024;
+                    a0[i] = ((up[2 * i + iu] + cur[2 * i + iu]) << 2) - 1024;
+                    a1[i] = ((up[2 * i + iv] + cur[2 * i + iv]) << 2) - 1024;
                 }
             }
             row_simd(y, a0, a1, d, w, &K_LIMITED);
@@ -103,8 +119,8 @@ int port_nv12_to_bgr24(const uint8_t *Y, int sy, const uint8_t *UV, int suv, int
             if (k0 == k1) a = 0;
             const uint8_t *r0 = UV + (size_t)k0 * suv, *r1 = UV + (size_t)k1 * suv;
             for (int i = 0; i < w / 2; i++) {
-                a0[i] = (r0[2 * i] * (4096 - a) + r1[2 * i] * a + 2048) >> 12;
-                a1[i] = (r0[2 * i + 1] * (4096 - a) + r1[2 * i + 1] * a + 2048) >> 12;
+                a0[i] = (r0[2 * i + iu] * (4096 - a) + r1[2 * i + iu] * a + 2048) >> 12;
+                a1[i] = (r0[2 * i + iv] * (4096 - a) + r1[2 * i + iv] * a + 2048) >> 12;
             }
             row_cpath(y, a0, a1, d, w);
         }

@@ -30,6 +30,27 @@ def test_header_symbols_are_exported_and_bound():
     assert not extra, f"exported but undeclared: {extra}"
 
 
+def test_header_is_plain_c():
+    """The boundary is a C ABI: the header must compile as C99 on its own, and a C caller must link."""
+    import shutil
+    import tempfile
+    gcc = shutil.which("gcc")
+    if not gcc:
+        pytest.skip("no gcc")
+    with tempfile.TemporaryDirectory() as d:
+        src = os.path.join(d, "t.c")
+        with open(src, "w") as f:
+            f.write('#include "vepb200.h"\n#include <stdio.h>\n'
+                    'int main(void){ vep_frame_desc d; vep_frame_meta m; (void)d; (void)m;\n'
+                    ' printf("%d %s %d\\n", vep_abi_version(), vep_status_name(VEP_ERR_BUSY), (int)sizeof(vep_frame_desc)); return 0; }\n')
+        exe = os.path.join(d, "t")
+        lib_dir = os.path.dirname(_abi.LIB_PATH)
+        subprocess.check_call([gcc, "-std=c99", "-Wall", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"), src, "-o", exe,
+                               "-L", lib_dir, "-lvepb200", f"-Wl,-rpath,{lib_dir}"])
+        out = subprocess.check_output([exe], text=True).split()
+        assert out == ["1", "VEP_ERR_BUSY", "72"]
+
+
 def test_abi_version_and_status_names():
     L = _abi.lib()
     assert L.vep_abi_version() == 1

@@ -62,7 +62,10 @@ def test_exhaustive_yuv_triples_planar_both_ranges(path):
             assert np.array_equal(got[r0:r0 + 512], want), (fmt, r0)
 
 
-@pytest.mark.parametrize("fmt", ["yuv420p", "yuvj420p", "nv12"])
+ALL_FORMATS = ["yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p"]
+
+
+@pytest.mark.parametrize("fmt", ALL_FORMATS)
 def test_seeded_random_config_sizes(path, fmt):
     for (w, h) in ((640, 480), (1280, 720), (1920, 1080), (3840, 2160)):
         for seed in (1, 2):
@@ -70,17 +73,17 @@ def test_seeded_random_config_sizes(path, fmt):
             assert np.array_equal(gpu_convert(path, fmt, planes), F.to_bgr24(fmt, planes)), (fmt, w, h, seed)
 
 
-@pytest.mark.parametrize("fmt", ["yuv420p", "yuvj420p", "nv12"])
+@pytest.mark.parametrize("fmt", ALL_FORMATS)
 def test_ragged_geometries_take_the_generic_path(path, fmt):
     for w in (2, 6, 14, 18, 30, 34, 62, 130, 510, 514, 642, 1922):
         for h in (2, 4, 8, 10, 18, 50):
-            if fmt == "nv12" and h < 8:
+            if fmt in ("nv12", "nv21") and h < 8:
                 continue
             planes = make_planes(fmt, w, h, 31 * w + h)
             assert np.array_equal(gpu_convert(path, fmt, planes), F.to_bgr24(fmt, planes)), (fmt, w, h)
 
 
-@pytest.mark.parametrize("fmt", ["yuv420p", "nv12"])
+@pytest.mark.parametrize("fmt", ["yuv420p", "nv12", "nv21", "yuvj422p"])
 def test_fast_path_widths_and_partial_segments(path, fmt):
     # multiples of 16 around the 512-px segment boundary: full, partial and single-lane segments
     for w in (16, 32, 496, 512, 528, 1008, 1024, 1040, 2048, 4096):
@@ -92,7 +95,8 @@ def test_live_libswscale_agrees_on_the_box(path):
     if not L.available():
         pytest.skip("bundled libswscale not found")
     assert L.on_simd_path()
-    for fmt, w, h in (("yuv420p", 1920, 1080), ("yuvj420p", 640, 480), ("nv12", 1280, 720), ("yuv420p", 50, 6)):
+    for fmt, w, h in (("yuv420p", 1920, 1080), ("yuvj420p", 640, 480), ("nv12", 1280, 720), ("yuv420p", 50, 6),
+                      ("nv21", 1920, 1080), ("yuv422p", 1280, 720), ("yuvj422p", 1920, 1080), ("yuvj422p", 50, 6)):
         planes = make_planes(fmt, w, h, 77)
         assert np.array_equal(gpu_convert(path, fmt, planes), L.to_bgr24(fmt, planes, w, h)), (fmt, w, h)
 
@@ -188,7 +192,8 @@ def test_persistent_tma_kernel_bit_identical(golden_pixels, small_frames):
             for fmt, w, h, seed, planes, want in small_frames:
                 assert np.array_equal(gpu_convert(p, fmt, planes), want), (fmt, w, h)
             for fmt, w, h in (("yuv420p", 16, 8), ("yuv420p", 48, 8), ("nv12", 528, 16), ("yuvj420p", 1040, 8), ("nv12", 32, 8),
-                              ("yuv420p", 64, 8), ("yuv420p", 496, 4), ("nv12", 18, 10)):
+                              ("yuv420p", 64, 8), ("yuv420p", 496, 4), ("nv12", 18, 10), ("nv21", 1280, 720), ("nv21", 48, 8),
+                              ("yuvj422p", 640, 480), ("yuv422p", 50, 6)):
                 planes = make_planes(fmt, w, h, w + h)
                 assert np.array_equal(gpu_convert(p, fmt, planes), F.to_bgr24(fmt, planes)), (fmt, w, h)
             # a mixed batch in one launch: bulk, vector and generic frames together
@@ -233,14 +238,16 @@ def test_tick_kernel_variants_bit_identical(env, small_frames):
         for fmt, w, h, seed, planes, want in small_frames:
             assert np.array_equal(gpu_convert(p, fmt, planes), want), (env, fmt, w, h)
         for fmt, w, h in (("yuv420p", 1920, 1080), ("nv12", 1920, 1080), ("yuvj420p", 640, 480), ("yuv420p", 528, 6), ("nv12", 1040, 10),
-                          ("yuv420p", 16, 2), ("nv12", 3840, 2160), ("yuv420p", 642, 482), ("nv12", 64, 14)):
+                          ("yuv420p", 16, 2), ("nv12", 3840, 2160), ("yuv420p", 642, 482), ("nv12", 64, 14),
+                          ("nv21", 1280, 720), ("yuvj422p", 1280, 720), ("yuv422p", 528, 6), ("nv21", 38, 12), ("yuvj422p", 50, 6)):
             planes = make_planes(fmt, w, h, w + h)
             assert np.array_equal(gpu_convert(p, fmt, planes), F.to_bgr24(fmt, planes)), (env, fmt, w, h)
         # 40 frames in one launch (128-entry parameter table) and 150 frames (falls back to the device table)
         for n in (40, 150):
             descs, keep = [], []
             for i in range(n):
-                fmt, w, h = (("yuv420p", 320, 240), ("nv12", 352, 288), ("yuvj420p", 160, 120), ("yuv420p", 50, 6))[i % 4]
+                fmt, w, h = (("yuv420p", 320, 240), ("nv12", 352, 288), ("yuvj420p", 160, 120), ("yuv420p", 50, 6),
+                             ("yuvj422p", 320, 240), ("nv21", 64, 48))[i % 6]
                 planes = make_planes(fmt, w, h, i)
                 t = [torch.from_numpy(q).cuda() for q in planes]
                 out = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")

@@ -28,7 +28,8 @@ def path():
 
 
 def test_to_ndarray_drop_in(path):
-    for fmt, w, h in (("yuv420p", 640, 480), ("yuvj420p", 1280, 720), ("nv12", 1920, 1080), ("yuv420p", 50, 6)):
+    for fmt, w, h in (("yuv420p", 640, 480), ("yuvj420p", 1280, 720), ("nv12", 1920, 1080), ("yuv420p", 50, 6),
+                      ("yuvj422p", 1280, 720), ("yuv422p", 50, 6), ("nv21", 640, 480)):
         planes = make_planes(fmt, w, h, 3)
         img = to_ndarray_bgr24(path, fmt, planes)
         assert img.dtype == np.uint8 and img.shape == (h, w, 3) and img.flags["C_CONTIGUOUS"]

@@ -41,7 +41,7 @@ def test_small_fixtures_numpy_and_c_port(small_frames):
         assert np.array_equal(P.to_bgr24(fmt, planes), out), (fmt, w, h)
 
 
-@pytest.mark.parametrize("row", range(21))
+@pytest.mark.parametrize("row", range(30))
 def test_numpy_restatement_matches_golden_table(golden_pixels, row):
     rows = golden_pixels["rows"]
     if row >= len(rows):
@@ -58,7 +58,8 @@ def test_numpy_restatement_matches_golden_table(golden_pixels, row):
 
 
 def test_c_port_matches_numpy_at_config_sizes():
-    for fmt, w, h in (("yuv420p", 1920, 1080), ("yuvj420p", 1280, 720), ("nv12", 1920, 1080), ("nv12", 642, 10)):
+    for fmt, w, h in (("yuv420p", 1920, 1080), ("yuvj420p", 1280, 720), ("nv12", 1920, 1080), ("nv12", 642, 10),
+                      ("nv21", 1280, 720), ("yuv422p", 642, 10), ("yuvj422p", 1920, 1080)):
         planes = make_planes(fmt, w, h, 3)
         assert np.array_equal(P.to_bgr24(fmt, planes), F.to_bgr24(fmt, planes)), (fmt, w, h)
 
@@ -106,10 +107,10 @@ def test_live_library_reproduces_survey_checksums(golden_pixels, fmt, w, h, seed
 
 @needs_live
 def test_live_vs_restatement_ragged_widths_and_heights():
-    for fmt in ("yuv420p", "yuvj420p", "nv12"):
+    for fmt in ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p"):
         for w in (2, 6, 14, 16, 18, 30, 34, 62, 130, 642):
             for h in (2, 4, 8, 10, 18):
-                if fmt == "nv12" and h < 8:
+                if fmt in ("nv12", "nv21") and h < 8:
                     continue
                 planes = make_planes(fmt, w, h, 1000 * w + h)
                 assert np.array_equal(L.to_bgr24(fmt, planes, w, h), F.to_bgr24(fmt, planes)), (fmt, w, h)

@@ -24,7 +24,7 @@ from video_edge_ai_proxy_b200.synth import make_planes  # noqa: E402
 
 FIRST = [("yuv420p", 1920, 1080, 1), ("nv12", 1280, 720, 2), ("yuvj420p", 640, 480, 3), ("yuv420p", 50, 6, 4),
          ("nv12", 642, 10, 5), ("yuv420p", 1920, 1080, 6), ("yuv420p", 528, 8, 7)]
-SECOND = [("nv12", 1920, 1080, 11), ("yuv420p", 640, 480, 12), ("yuvj420p", 34, 4, 13)]
+SECOND = [("nv12", 1920, 1080, 11), ("yuv420p", 640, 480, 12), ("yuvj420p", 34, 4, 13), ("yuvj422p", 640, 480, 14), ("nv21", 320, 240, 15)]
 
 
 def _batch(specs, fill):

@@ -93,11 +93,11 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1) 
     for (int i = 0; i < n; ++i) {
         const vep_frame_desc &s = d[i];
         if (!s.convert) continue;
-        if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_NV12) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
+        if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_YUVJ422P) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
         const int w = s.width, h = s.height;
         if (w <= 0 || h <= 0 || w > kMaxDim || h > kMaxDim || (w & 1) || (h & 1))
             return fail(VEP_ERR_GEOMETRY, "desc %d: %dx%d — 4:2:0 needs even, positive dimensions <= %d", i, w, h, kMaxDim);
-        const bool nv12 = s.fmt == VEP_FMT_NV12;
+        const bool nv12 = vep::fmt_is_semiplanar(s.fmt);
         if (nv12 && h < 8) return fail(VEP_ERR_GEOMETRY, "desc %d: nv12 height %d < 8 (swscale changes its vertical chroma filter there)", i, h);
         if (!s.plane[0] || !s.plane[1] || (!nv12 && !s.plane[2]) || !s.dst) return fail(VEP_ERR_INVALID_ARG, "desc %d: null plane or dst", i);
         const int cw = nv12 ? w : w / 2;
@@ -112,6 +112,7 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1) 
                          (nv12 || (aligned(f.c1, 8) && f.sc1 % 8 == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
         const bool bulk = vec && (w % 32 == 0) && aligned(f.c0, 16) && f.sc0 % 16 == 0 && (nv12 || (aligned(f.c1, 16) && f.sc1 % 16 == 0));
         f.fast = bulk ? vep::PATH_BULK : vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;
+        f.fast_tbl = vep::fmt_is_422(s.fmt) ? vep::PATH_GENERIC : f.fast;   // only the tick kernel has a vector path for 4:2:2
         f.segs = (w + vep::kSegPx - 1) / vep::kSegPx;
         f.segs_magic = f.segs == 1 ? 0u : (uint32_t)((((uint64_t)1 << 32) + f.segs - 1) / f.segs);
         f.item_begin = t.total_items;
@@ -121,7 +122,7 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1) 
         t.tick_cta_begin.push_back(tick_ctas);
         if (f.fast != vep::PATH_GENERIC) tick_ctas += (f.segs * ((h / 2 + rpt - 1) / rpt) + vep::kWarpsPerCta - 1) / vep::kWarpsPerCta;
         else tick_ctas += ((w / 2) * (h / 2) + vep::kGenericBlocksPerCta - 1) / vep::kGenericBlocksPerCta;
-        if (f.fast != vep::PATH_GENERIC) {
+        if (f.fast_tbl != vep::PATH_GENERIC) {
             items = f.segs * (h / 2);
             for (int it = 0; it < items; it += vep::kWarpsPerCta) t.work.push_back(CtaWork{fi, it});
         } else {
@@ -131,7 +132,7 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1) 
         }
         if ((int64_t)t.total_items + items > (int64_t)1 << 30) return fail(VEP_ERR_INVALID_ARG, "batch too large");
         t.total_items += items;
-        t.alg_bytes += (int64_t)w * h * 9 / 2;
+        t.alg_bytes += vep::fmt_is_422(s.fmt) ? (int64_t)w * h * 5 : (int64_t)w * h * 9 / 2;   // 4:2:2 reads 2 B/px
         t.n_converted++;
     }
     FrameDev sentinel{};
@@ -541,9 +542,9 @@ static Stream *find_stream(vep_ctx *c, int id) {
 
 extern "C" int vep_stream_open(vep_ctx *c, int stream_id, int fmt, int w, int h, int ring_depth) {
     if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
-    if (fmt < VEP_FMT_YUV420P || fmt > VEP_FMT_NV12) return fail(VEP_ERR_INVALID_ARG, "unknown fmt %d", fmt);
+    if (fmt < VEP_FMT_YUV420P || fmt > VEP_FMT_YUVJ422P) return fail(VEP_ERR_INVALID_ARG, "unknown fmt %d", fmt);
     if (w <= 0 || h <= 0 || w > kMaxDim || h > kMaxDim || (w & 1) || (h & 1)) return fail(VEP_ERR_GEOMETRY, "%dx%d: need even, positive dimensions", w, h);
-    if (fmt == VEP_FMT_NV12 && h < 8) return fail(VEP_ERR_GEOMETRY, "nv12 height %d < 8", h);
+    if (vep::fmt_is_semiplanar(fmt) && h < 8) return fail(VEP_ERR_GEOMETRY, "nv12/nv21 height %d < 8", h);
     if (ring_depth < 1) ring_depth = 1;
     if (ring_depth > 64) return fail(VEP_ERR_INVALID_ARG, "ring_depth %d > 64", ring_depth);
     DeviceGuard g(c->device);
@@ -556,8 +557,9 @@ extern "C" int vep_stream_open(vep_ctx *c, int stream_id, int fmt, int w, int h,
     s->id = stream_id; s->fmt = fmt; s->w = w; s->h = h; s->ring = ring_depth;
     const size_t ysz = (size_t)w * h;
     s->off_c0 = align_up(ysz, 256);
-    if (fmt == VEP_FMT_NV12) { s->off_c1 = 0; s->in_bytes = s->off_c0 + ysz / 2; }
-    else { s->off_c1 = s->off_c0 + align_up(ysz / 4, 256); s->in_bytes = s->off_c1 + ysz / 4; }
+    const size_t csz = vep::fmt_is_422(fmt) ? ysz / 2 : ysz / 4;   // bytes of one planar chroma plane
+    if (vep::fmt_is_semiplanar(fmt)) { s->off_c1 = 0; s->in_bytes = s->off_c0 + ysz / 2; }
+    else { s->off_c1 = s->off_c0 + align_up(csz, 256); s->in_bytes = s->off_c1 + csz; }
     s->out_bytes = ysz * 3;
     s->in_slot = align_up(s->in_bytes, 4096);
     s->out_slot = align_up(kHdrRoom + s->out_bytes + kTrailerRoom, 4096);
@@ -616,8 +618,9 @@ static int claim_slot(Stream *s) {
 }
 
 static void plane_ptrs(Stream *s, uint8_t *base, uint8_t *pl[3], int32_t st[3]) {
-    pl[0] = base; pl[1] = base + s->off_c0; pl[2] = s->fmt == VEP_FMT_NV12 ? nullptr : base + s->off_c1;
-    st[0] = s->w; st[1] = s->fmt == VEP_FMT_NV12 ? s->w : s->w / 2; st[2] = s->fmt == VEP_FMT_NV12 ? 0 : s->w / 2;
+    const bool semi = vep::fmt_is_semiplanar(s->fmt);
+    pl[0] = base; pl[1] = base + s->off_c0; pl[2] = semi ? nullptr : base + s->off_c1;
+    st[0] = s->w; st[1] = semi ? s->w : s->w / 2; st[2] = semi ? 0 : s->w / 2;
 }
 
 extern "C" int vep_acquire_input(vep_ctx *c, int stream_id, uint8_t *plane_out[3], int32_t stride_out[3]) {
@@ -683,9 +686,11 @@ extern "C" int vep_submit(vep_ctx *c, int stream_id, const uint8_t *const plane[
         __atomic_add_fetch(&c->stats.frames_offered, 1, __ATOMIC_RELAXED);
         return VEP_OK;
     }
-    if (!plane || !stride || !plane[0] || !plane[1] || (s->fmt != VEP_FMT_NV12 && !plane[2])) return fail(VEP_ERR_INVALID_ARG, "null plane");
-    const int cw = s->fmt == VEP_FMT_NV12 ? s->w : s->w / 2;
-    if (stride[0] < s->w || stride[1] < cw || (s->fmt != VEP_FMT_NV12 && stride[2] < cw)) return fail(VEP_ERR_GEOMETRY, "stride smaller than row");
+    const bool semi = vep::fmt_is_semiplanar(s->fmt);
+    if (!plane || !stride || !plane[0] || !plane[1] || (!semi && !plane[2])) return fail(VEP_ERR_INVALID_ARG, "null plane");
+    const int cw = semi ? s->w : s->w / 2;
+    const int crows = vep::fmt_is_422(s->fmt) ? s->h : s->h / 2;
+    if (stride[0] < s->w || stride[1] < cw || (!semi && stride[2] < cw)) return fail(VEP_ERR_GEOMETRY, "stride smaller than row");
     uint8_t *pl[3];
     int32_t st[3];
     {
@@ -696,8 +701,8 @@ extern "C" int vep_submit(vep_ctx *c, int stream_id, const uint8_t *const plane[
     }
     // the copy runs outside the lock: one producer per stream
     copy_plane(pl[0], st[0], plane[0], stride[0], s->w, s->h);
-    copy_plane(pl[1], st[1], plane[1], stride[1], cw, s->h / 2);
-    if (s->fmt != VEP_FMT_NV12) copy_plane(pl[2], st[2], plane[2], stride[2], cw, s->h / 2);
+    copy_plane(pl[1], st[1], plane[1], stride[1], cw, crows);
+    if (!semi) copy_plane(pl[2], st[2], plane[2], stride[2], cw, crows);
     return vep_commit_input(c, stream_id, meta);
 }
 
@@ -735,8 +740,9 @@ extern "C" int vep_tick_begin(vep_ctx *c, int *n_frames) {
             CUDA_TRY(cudaMemcpyAsync(sl.d_in, sl.h_in, s->in_bytes, cudaMemcpyHostToDevice, s->cs_in));
             c->stats.h2d_bytes += (int64_t)s->in_bytes;
             vep_frame_desc d{};
-            d.plane[0] = sl.d_in; d.plane[1] = sl.d_in + s->off_c0; d.plane[2] = s->fmt == VEP_FMT_NV12 ? nullptr : sl.d_in + s->off_c1;
-            d.stride[0] = s->w; d.stride[1] = s->fmt == VEP_FMT_NV12 ? s->w : s->w / 2; d.stride[2] = s->fmt == VEP_FMT_NV12 ? 0 : s->w / 2;
+            const bool semi = vep::fmt_is_semiplanar(s->fmt);
+            d.plane[0] = sl.d_in; d.plane[1] = sl.d_in + s->off_c0; d.plane[2] = semi ? nullptr : sl.d_in + s->off_c1;
+            d.stride[0] = s->w; d.stride[1] = semi ? s->w : s->w / 2; d.stride[2] = semi ? 0 : s->w / 2;
             d.dst = sl.d_out; d.dst_stride = 3 * s->w; d.width = s->w; d.height = s->h; d.fmt = s->fmt; d.convert = 1;
             descs.push_back(d);
             write_framing(s, sl);
@@ -890,11 +896,11 @@ static CtaWork g_noalloc_h_work[VEP_NOALLOC_MAX_CTAS];
 
 // Validation + table row for one descriptor; mirrors build_tables() without touching the heap.
 static int noalloc_frame(const vep_frame_desc &s, int i, FrameDev &f) {
-    if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_NV12) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
+    if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_YUVJ422P) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
     const int w = s.width, h = s.height;
     if (w <= 0 || h <= 0 || w > kMaxDim || h > kMaxDim || (w & 1) || (h & 1))
         return fail(VEP_ERR_GEOMETRY, "desc %d: %dx%d — 4:2:0 needs even, positive dimensions <= %d", i, w, h, kMaxDim);
-    const bool nv12 = s.fmt == VEP_FMT_NV12;
+    const bool nv12 = vep::fmt_is_semiplanar(s.fmt);
     if (nv12 && h < 8) return fail(VEP_ERR_GEOMETRY, "desc %d: nv12 height %d < 8", i, h);
     if (!s.plane[0] || !s.plane[1] || (!nv12 && !s.plane[2]) || !s.dst) return fail(VEP_ERR_INVALID_ARG, "desc %d: null plane or dst", i);
     const int cw = nv12 ? w : w / 2;
@@ -908,6 +914,8 @@ static int noalloc_frame(const vep_frame_desc &s, int i, FrameDev &f) {
     const bool vec = (w % 16 == 0) && aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
                      (nv12 || (aligned(f.c1, 8) && f.sc1 % 8 == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
     f.fast = vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;   // the table-driven kernel knows these two paths
+    if (vep::fmt_is_422(s.fmt)) f.fast = vep::PATH_GENERIC;   // ... and converts 4:2:2 on the scalar one
+    f.fast_tbl = f.fast;
     f.segs = (w + vep::kSegPx - 1) / vep::kSegPx;
     return VEP_OK;
 }

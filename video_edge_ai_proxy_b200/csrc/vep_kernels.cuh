@@ -17,13 +17,19 @@
 
 namespace vep {
 
-constexpr int kWarpsPerCta = 8;
+#ifndef VEP_WARPS_PER_CTA
+#define VEP_WARPS_PER_CTA 8
+#endif
+constexpr int kWarpsPerCta = VEP_WARPS_PER_CTA;   // 8 measured best (4: same overlapped, strict order within 1 %)
 constexpr int kThreads = kWarpsPerCta * 32;
 constexpr int kSegPx = 512;                       // pixels per warp item row (32 lanes x 16 px)
 constexpr int kSegBytes = kSegPx * 3;             // 1536 output bytes per row of an item
 constexpr int kGenericBlocksPerCta = 1024;        // 2x2 blocks per CTA on the generic path
 
-enum : int { FMT_YUV420P = 0, FMT_YUVJ420P = 1, FMT_NV12 = 2 };
+enum : int { FMT_YUV420P = 0, FMT_YUVJ420P = 1, FMT_NV12 = 2, FMT_NV21 = 3, FMT_YUV422P = 4, FMT_YUVJ422P = 5 };
+__host__ __device__ constexpr bool fmt_is_semiplanar(int f) { return f == FMT_NV12 || f == FMT_NV21; }
+__host__ __device__ constexpr bool fmt_is_422(int f) { return f == FMT_YUV422P || f == FMT_YUVJ422P; }
+__host__ __device__ constexpr bool fmt_is_full_range(int f) { return f == FMT_YUVJ420P || f == FMT_YUVJ422P; }
 
 enum : int { PATH_GENERIC = 0, PATH_VECTOR = 1, PATH_BULK = 2 };
 
@@ -38,7 +44,7 @@ struct __align__(16) FrameDev {   // 80 bytes, one per converted frame (+1 senti
     int32_t item_begin;           // first item of this frame in the launch-wide item space (sentinel: total)
     int32_t segs;                 // 512-px segments per row pair
     uint32_t segs_magic;          // ceil(2^32 / segs): rp = umulhi(local, magic) for local < 2^20
-    int32_t pad_;
+    int32_t fast_tbl;             // PATH_* as seen by the table-driven and persistent kernels (4:2:2 -> generic there)
 };
 struct CtaWork {                  // 8 bytes per CTA
     int32_t frame;                // index into the FrameDev table
@@ -186,6 +192,21 @@ __device__ __forceinline__ void compute_planar(const uint4 &ya, const uint4 &yb,
         luma4_a<FULL>(word_of(yb, g), P, Q, o1[3 * g], o1[3 * g + 1], o1[3 * g + 2]);
     }
 }
+// 4:2:2: each luma row has its own chroma row (no vertical sharing); one row at a time
+template <bool FULL>
+__device__ __forceinline__ void compute_planar_row(const uint4 &y, const uint2 &uu, const uint2 &vv, uint32_t (&o)[12]) {
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        const uint32_t uw = g < 2 ? uu.x : uu.y, vw = g < 2 ? vv.x : vv.y;
+        const int b = (g & 1) * 2;
+        const ChromaPair P = chroma_a<FULL>(byte_of(uw, b), byte_of(vw, b));
+        const ChromaPair Q = chroma_a<FULL>(b == 2 ? (uw >> 24) : byte_of(uw, 1), b == 2 ? (vw >> 24) : byte_of(vw, 1));
+        luma4_a<FULL>(word_of(y, g), P, Q, o[3 * g], o[3 * g + 1], o[3 * g + 2]);
+    }
+}
+__device__ __forceinline__ uint32_t swap_pairs(uint32_t w) { return prmt(w, 0, 0x2301); }   // V,U -> U,V in both pairs
+__device__ __forceinline__ uint4 swap_pairs(const uint4 &v) { return make_uint4(swap_pairs(v.x), swap_pairs(v.y), swap_pairs(v.z), swap_pairs(v.w)); }
+
 template <bool FULL>
 __device__ __forceinline__ void lane_planar(const FrameDev &f, int rp, int x, uint32_t (&o0)[12], uint32_t (&o1)[12]) {
     const uint4 ya = ld_stream_v4(f.y + (size_t)(2 * rp) * f.sy + x);
@@ -222,8 +243,9 @@ __device__ __forceinline__ void lane_nv12(const FrameDev &f, int rp, int x, uint
     const uint4 ya = ld_stream_v4(f.y + (size_t)(2 * rp) * f.sy + x);
     const uint4 yb = ld_stream_v4(f.y + (size_t)(2 * rp + 1) * f.sy + x);
     const int up = rp > 0 ? rp - 1 : 0;
-    const uint4 cu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)rp * f.sc0 + x));   // u0 v0 u1 v1 ...
-    const uint4 pu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)up * f.sc0 + x));   // row above (L2/L1 hit)
+    uint4 cu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)rp * f.sc0 + x));   // u0 v0 u1 v1 ...
+    uint4 pu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)up * f.sc0 + x));   // row above (L2/L1 hit)
+    if (f.fmt == FMT_NV21) { cu = swap_pairs(cu); pu = swap_pairs(pu); }
     compute_nv12(ya, yb, cu, pu, rp == (f.h >> 1) - 1, o0, o1);   // rows H-2, H-1: swscale leaves its SIMD output stage
 }
 
@@ -246,21 +268,24 @@ __device__ __forceinline__ void px_b(int Y, int u, int v, uint8_t *d) {
 __device__ __forceinline__ void generic_block(const FrameDev &f, int bx, int by) {
     const uint8_t *y0 = f.y + (size_t)(2 * by) * f.sy + 2 * bx, *y1 = y0 + f.sy;
     uint8_t *d0 = f.dst + (size_t)(2 * by) * f.sd + 6 * bx, *d1 = d0 + f.sd;
-    if (f.fmt != FMT_NV12) {
-        const int Uw = ((int)f.c0[(size_t)by * f.sc0 + bx] << 3) - 1024;
-        const int Vw = ((int)f.c1[(size_t)by * f.sc1 + bx] << 3) - 1024;
-        if (f.fmt == FMT_YUVJ420P) {
+    if (!fmt_is_semiplanar(f.fmt)) {
+        // 4:2:0: one chroma row per row pair; 4:2:2: chroma row j for luma row j
+        const int r0 = fmt_is_422(f.fmt) ? 2 * by : by, r1 = fmt_is_422(f.fmt) ? 2 * by + 1 : by;
+        const int Uw = ((int)f.c0[(size_t)r0 * f.sc0 + bx] << 3) - 1024, Vw = ((int)f.c1[(size_t)r0 * f.sc1 + bx] << 3) - 1024;
+        const int Ux = ((int)f.c0[(size_t)r1 * f.sc0 + bx] << 3) - 1024, Vx = ((int)f.c1[(size_t)r1 * f.sc1 + bx] << 3) - 1024;
+        if (fmt_is_full_range(f.fmt)) {
             px_a<true>(y0[0], Uw, Vw, d0); px_a<true>(y0[1], Uw, Vw, d0 + 3);
-            px_a<true>(y1[0], Uw, Vw, d1); px_a<true>(y1[1], Uw, Vw, d1 + 3);
+            px_a<true>(y1[0], Ux, Vx, d1); px_a<true>(y1[1], Ux, Vx, d1 + 3);
         } else {
             px_a<false>(y0[0], Uw, Vw, d0); px_a<false>(y0[1], Uw, Vw, d0 + 3);
-            px_a<false>(y1[0], Uw, Vw, d1); px_a<false>(y1[1], Uw, Vw, d1 + 3);
+            px_a<false>(y1[0], Ux, Vx, d1); px_a<false>(y1[1], Ux, Vx, d1 + 3);
         }
         return;
     }
     const int up = by > 0 ? by - 1 : 0;
     const uint8_t *c = f.c0 + (size_t)by * f.sc0 + 2 * bx, *p = f.c0 + (size_t)up * f.sc0 + 2 * bx;
-    const int u = c[0], v = c[1], pu = p[0], pv = p[1];
+    const int iu = f.fmt == FMT_NV21 ? 1 : 0;
+    const int u = c[iu], v = c[1 - iu], pu = p[iu], pv = p[1 - iu];
     if (by != (f.h >> 1) - 1) {
         const int Ue = ((pu + u) << 2) - 1024, Ve = ((pv + v) << 2) - 1024;
         const int Uo = (u << 3) - 1024, Vo = (v << 3) - 1024;
@@ -284,7 +309,7 @@ yuv_to_bgr24_batched(const FrameDev *__restrict__ frames, const CtaWork *__restr
     const CtaWork cw = work[blockIdx.x];
     const FrameDev f = frames[cw.frame];
 
-    if (f.fast == PATH_GENERIC) {
+    if (f.fast_tbl == PATH_GENERIC) {
         const int bw = f.w >> 1, nblk = bw * (f.h >> 1);
         for (int q = cw.first + threadIdx.x; q < min(cw.first + kGenericBlocksPerCta, nblk); q += kThreads)
             generic_block(f, q % bw, q / bw);
@@ -303,7 +328,7 @@ yuv_to_bgr24_batched(const FrameDev *__restrict__ frames, const CtaWork *__restr
     if (active) {
         if (f.fmt == FMT_YUV420P) lane_planar<false>(f, rp, x, o0, o1);
         else if (f.fmt == FMT_YUVJ420P) lane_planar<true>(f, rp, x, o0, o1);
-        else lane_nv12(f, rp, x, o0, o1);
+        else lane_nv12(f, rp, x, o0, o1);   // nv12 / nv21 (4:2:2 frames never reach here: fast_tbl is generic)
     }
     uint8_t *g0 = f.dst + (size_t)(2 * rp) * f.sd + (size_t)seg * kSegBytes;
     uint8_t *g1 = g0 + f.sd;
@@ -421,7 +446,8 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     // ---- all loads first ----
     uint4 ya[RPT], yb[RPT], ca[RPT];   // ca: planar {U.lo,U.hi,V.lo,V.hi}; nv12: the 16 interleaved chroma bytes
     uint4 pu = make_uint4(0, 0, 0, 0);
-    const bool nv12 = f.fmt == FMT_NV12;
+    const bool nv12 = fmt_is_semiplanar(f.fmt);
+    const int cshift = fmt_is_422(f.fmt) ? 1 : 0;           // 4:2:2: chroma row of luma row j is row j, not j/2
     if (active) {
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
@@ -431,19 +457,38 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
             if (nv12) {
                 ca[r] = ld_stream_v4(f.c0 + (size_t)rp * f.sc0 + x);
             } else {
-                const uint2 uu = ld_stream_v2(f.c0 + (size_t)rp * f.sc0 + (x >> 1));
-                const uint2 vv = ld_stream_v2(f.c1 + (size_t)rp * f.sc1 + (x >> 1));
+                const uint2 uu = ld_stream_v2(f.c0 + (size_t)(rp << cshift) * f.sc0 + (x >> 1));
+                const uint2 vv = ld_stream_v2(f.c1 + (size_t)(rp << cshift) * f.sc1 + (x >> 1));
                 ca[r] = make_uint4(uu.x, uu.y, vv.x, vv.y);
             }
         }
         if (nv12) pu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)(rp0 > 0 ? rp0 - 1 : 0) * f.sc0 + x));
+        if (f.fmt == FMT_NV21) {                            // V first: swap each pair once, then it is NV12
+            pu = swap_pairs(pu);
+#pragma unroll
+            for (int r = 0; r < RPT; ++r) ca[r] = swap_pairs(ca[r]);
+        }
     }
 
 #pragma unroll
     for (int r = 0; r < RPT; ++r) {
         const int rp = rp0 + r;
         if (rp >= hp) break;                                // warp-uniform
-        if (active) {
+        if (active && cshift) {
+            // 4:2:2: the odd luma row has a chroma row of its own.  One row at a time (park it, then the next)
+            // keeps this secondary format from raising the register count of the 4:2:0 path.
+            uint32_t o[12];
+            if (f.fmt == FMT_YUV422P) compute_planar_row<false>(ya[r], make_uint2(ca[r].x, ca[r].y), make_uint2(ca[r].z, ca[r].w), o);
+            else compute_planar_row<true>(ya[r], make_uint2(ca[r].x, ca[r].y), make_uint2(ca[r].z, ca[r].w), o);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) *reinterpret_cast<uint4 *>(t0 + lane * 48 + k * 16) = make_uint4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
+            const uint2 ub = ld_stream_v2(f.c0 + (size_t)(2 * rp + 1) * f.sc0 + (x >> 1));
+            const uint2 vb = ld_stream_v2(f.c1 + (size_t)(2 * rp + 1) * f.sc1 + (x >> 1));
+            if (f.fmt == FMT_YUV422P) compute_planar_row<false>(yb[r], ub, vb, o);
+            else compute_planar_row<true>(yb[r], ub, vb, o);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) *reinterpret_cast<uint4 *>(t1 + lane * 48 + k * 16) = make_uint4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
+        } else if (active) {
             uint32_t o0[12], o1[12];
             if (f.fmt == FMT_YUV420P) compute_planar<false>(ya[r], yb[r], make_uint2(ca[r].x, ca[r].y), make_uint2(ca[r].z, ca[r].w), o0, o1);
             else if (f.fmt == FMT_YUVJ420P) compute_planar<true>(ya[r], yb[r], make_uint2(ca[r].x, ca[r].y), make_uint2(ca[r].z, ca[r].w), o0, o1);
@@ -499,7 +544,7 @@ struct StageMeta {        // 32 bytes, written by lane 0 at issue time, read by 
     uint8_t *g0;          // first output row of the item
     int32_t sd;           // output stride
     int32_t seg_bytes;    // visible bytes per output row of this item (3 * pixels)
-    int32_t flags;        // bits 0-1 fmt, bit 2 nv12 tail rows, bits 3-4 path
+    int32_t flags;        // bits 0-2 fmt, bit 3 nv12/nv21 tail rows, bits 4-5 path
     int32_t fi;           // frame index
     int32_t a, b;         // vector path: rp, seg;  generic path: a = first 2x2 block
 };
@@ -555,32 +600,32 @@ yuv_to_bgr24_persistent(const FrameDev *__restrict__ frames, int total_items) {
         while (item >= __ldg(&frames[fi + 1].item_begin)) ++fi;
         const FrameDev *f = frames + fi;
         const int4 q2 = __ldg(reinterpret_cast<const int4 *>(&f->w));           // w, h, fmt, path
-        const int4 q3 = __ldg(reinterpret_cast<const int4 *>(&f->item_begin));  // item_begin, segs, magic
-        const int w = q2.x, h = q2.y, fmt = q2.z, path = q2.w;
+        const int4 q3 = __ldg(reinterpret_cast<const int4 *>(&f->item_begin));  // item_begin, segs, magic, fast_tbl
+        const int w = q2.x, h = q2.y, fmt = q2.z, path = q3.w;
         const int local = item - q3.x;
         if (path == PATH_GENERIC) {
-            if (lane == 0) { meta[s].flags = fmt | (path << 3); meta[s].fi = fi; meta[s].a = local * kGenericBlocksPerCta; }
+            if (lane == 0) { meta[s].flags = fmt | (path << 4); meta[s].fi = fi; meta[s].a = local * kGenericBlocksPerCta; }
             return;
         }
         const int segs = q3.y;
         const int rp = q3.z ? (int)__umulhi((uint32_t)local, (uint32_t)q3.z) : local;   // magic 0 <=> one segment per row
         const int seg = local - rp * segs;
         const int wseg = min(kSegPx, w - seg * kSegPx);
-        const int tail = (fmt == FMT_NV12 && rp == (h >> 1) - 1) ? 1 : 0;
+        const int tail = (fmt_is_semiplanar(fmt) && rp == (h >> 1) - 1) ? 1 : 0;
         if (lane == 0) {
             const int4 q1 = __ldg(reinterpret_cast<const int4 *>(&f->sy));      // sy, sc0, sc1, sd
             uint8_t *dst = const_cast<uint8_t *>(reinterpret_cast<const uint8_t *>(__ldg(reinterpret_cast<const unsigned long long *>(&f->dst))));
             meta[s].g0 = dst + (size_t)(2 * rp) * q1.w + (size_t)seg * kSegBytes;
             meta[s].sd = q1.w;
             meta[s].seg_bytes = 3 * wseg;
-            meta[s].flags = fmt | (tail << 2) | (path << 3);
+            meta[s].flags = fmt | (tail << 3) | (path << 4);
             meta[s].fi = fi; meta[s].a = rp; meta[s].b = seg;
             if (path == PATH_BULK) {
                 const uint8_t *y = reinterpret_cast<const uint8_t *>(__ldg(reinterpret_cast<const unsigned long long *>(&f->y)));
                 const uint8_t *c0 = reinterpret_cast<const uint8_t *>(__ldg(reinterpret_cast<const unsigned long long *>(&f->c0)));
                 const uint32_t bar = bar0 + 8 * s, st = stage0 + s * kStageBytes;
                 const uint8_t *yr = y + (size_t)(2 * rp) * q1.x + seg * kSegPx;
-                if (fmt == FMT_NV12) {
+                if (fmt_is_semiplanar(fmt)) {
                     mbar_expect_tx(bar, 4 * wseg);
                     bulk_g2s(st, yr, wseg, bar);
                     bulk_g2s(st + 512, yr + q1.x, wseg, bar);
@@ -607,7 +652,7 @@ yuv_to_bgr24_persistent(const FrameDev *__restrict__ frames, int total_items) {
     for (int item = w0; item < total_items; item += G, ++k) {
         const int s = k & 1;
         const StageMeta m = meta[s];            // broadcast read
-        const int fmt = m.flags & 3, path = (m.flags >> 3) & 3;
+        const int fmt = m.flags & 7, path = (m.flags >> 4) & 3;
         const uint8_t *st = base + s * kStageBytes;
 
         if (path == PATH_GENERIC) {
@@ -628,10 +673,11 @@ yuv_to_bgr24_persistent(const FrameDev *__restrict__ frames, int total_items) {
             if (active) {
                 const uint4 ya = *reinterpret_cast<const uint4 *>(st + lane * 16);
                 const uint4 yb = *reinterpret_cast<const uint4 *>(st + 512 + lane * 16);
-                if (fmt == FMT_NV12) {
-                    const uint4 cu = *reinterpret_cast<const uint4 *>(st + 1024 + lane * 16);
-                    const uint4 pu = *reinterpret_cast<const uint4 *>(st + 1536 + lane * 16);
-                    compute_nv12(ya, yb, cu, pu, (m.flags >> 2) & 1, o0, o1);
+                if (fmt_is_semiplanar(fmt)) {
+                    uint4 cu = *reinterpret_cast<const uint4 *>(st + 1024 + lane * 16);
+                    uint4 pu = *reinterpret_cast<const uint4 *>(st + 1536 + lane * 16);
+                    if (fmt == FMT_NV21) { cu = swap_pairs(cu); pu = swap_pairs(pu); }
+                    compute_nv12(ya, yb, cu, pu, (m.flags >> 3) & 1, o0, o1);
                 } else {
                     const uint2 uu = *reinterpret_cast<const uint2 *>(st + 1024 + lane * 8);
                     const uint2 vv = *reinterpret_cast<const uint2 *>(st + 1280 + lane * 8);

@@ -8,11 +8,11 @@ from __future__ import annotations
 
 import numpy as np
 
-FORMATS = ("yuv420p", "yuvj420p", "nv12")
+FORMATS = ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p")
 
 
 def make_planes(fmt: str, w: int, h: int, seed: int, dist: str = "uniform"):
-    """Return the plane tuple for one frame: (Y,U,V) for planar formats, (Y,UV) for nv12."""
+    """Return the plane tuple for one frame: (Y,U,V) for planar formats, (Y,UV) for nv12 / (Y,VU) for nv21."""
     if fmt not in FORMATS:
         raise ValueError(fmt)
     if w % 2 or h % 2:
@@ -24,13 +24,14 @@ def make_planes(fmt: str, w: int, h: int, seed: int, dist: str = "uniform"):
         lo_y, hi_y, lo_c, hi_c = 16, 236, 16, 241
     else:
         raise ValueError(dist)
+    ch = h if fmt in ("yuv422p", "yuvj422p") else h // 2      # 4:2:2 keeps every chroma row
     Y = rng.integers(lo_y, hi_y, (h, w), dtype=np.uint8)
-    U = rng.integers(lo_c, hi_c, (h // 2, w // 2), dtype=np.uint8)
-    V = rng.integers(lo_c, hi_c, (h // 2, w // 2), dtype=np.uint8)
-    if fmt == "nv12":
+    U = rng.integers(lo_c, hi_c, (ch, w // 2), dtype=np.uint8)
+    V = rng.integers(lo_c, hi_c, (ch, w // 2), dtype=np.uint8)
+    if fmt in ("nv12", "nv21"):
         UV = np.empty((h // 2, w), np.uint8)
-        UV[:, 0::2] = U
-        UV[:, 1::2] = V
+        UV[:, 0::2] = U if fmt == "nv12" else V
+        UV[:, 1::2] = V if fmt == "nv12" else U
         return (Y, UV)
     return (Y, U, V)
 
