@@ -151,6 +151,14 @@ class Converter:
         self._dst = (ctypes.c_void_p * 4)(self.dst.ctypes.data, None, None, None)
         self._dstr = (ctypes.c_int * 4)(self.sd, 0, 0, 0)
 
+    def renew_context(self):
+        """Free and re-create the SwsContext (PyAV makes a new reformatter for every decoded frame)."""
+        self._sws.sws_freeContext(self.ctx)
+        self.ctx = self._sws.sws_getContext(self.w, self.h, PIX_FMT[self.fmt], self.w, self.h, PIX_FMT["bgr24"],
+                                            SWS_BILINEAR, None, None, None)
+        if not self.ctx:
+            raise RuntimeError("sws_getContext failed")
+
     def load(self, planes):
         w, h = self.w, self.h
         self.y[:, :w] = planes[0]

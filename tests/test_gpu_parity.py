@@ -342,3 +342,39 @@ def test_rejections(path):
         path.convert_batch([d])
     assert e.value.status == _abi.VEP_ERR_GEOMETRY
     path.convert_batch([])          # empty batch is fine
+
+
+def test_random_geometry_fuzz_one_launch_per_round(path):
+    """Seeded fuzz: random formats, even sizes (biased to segment/vector boundaries), random row padding and
+    pointer offsets, 24 frames per launch — every visible byte equals the oracle, no byte outside is touched."""
+    rng = np.random.default_rng(2026)
+    widths = [2, 4, 14, 16, 18, 30, 32, 34, 48, 62, 64, 96, 130, 496, 510, 512, 514, 528, 1008, 1024, 1040, 1056, 1922]
+    for rnd in range(6):
+        descs, keep = [], []
+        for i in range(24):
+            fmt = ALL_FORMATS[int(rng.integers(len(ALL_FORMATS)))]
+            w = int(widths[int(rng.integers(len(widths)))])
+            h = int(rng.choice([2, 4, 6, 8, 10, 12, 18, 34, 50]))
+            if fmt in ("nv12", "nv21"):
+                h = max(h, 8)
+            pad = int(rng.choice([0, 0, 16, 32, 7, 48]))
+            off = int(rng.choice([0, 0, 16, 8, 3]))
+            planes = make_planes(fmt, w, h, 1000 * rnd + i)
+            bufs, ptrs, strides = [], [], []
+            for p in planes:
+                ph, pw = p.shape
+                buf = torch.full((ph * (pw + pad) + off + 64,), 0x33, dtype=torch.uint8, device="cuda")
+                view = buf[off:off + ph * (pw + pad)].view(ph, pw + pad)
+                view[:, :pw] = torch.from_numpy(p).cuda()
+                bufs.append(buf); ptrs.append(view.data_ptr()); strides.append(pw + pad)
+            dstride = 3 * w + pad
+            obuf = torch.full((h * dstride + off + 64,), 0x5A, dtype=torch.uint8, device="cuda")
+            descs.append(desc_from_device_ptrs(fmt, w, h, ptrs, strides, obuf.data_ptr() + off, dstride))
+            keep.append((fmt, w, h, pad, off, dstride, planes, bufs, obuf))
+        path.convert_batch(descs, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        for fmt, w, h, pad, off, dstride, planes, bufs, obuf in keep:
+            o = obuf.cpu().numpy()
+            rows = o[off:off + h * dstride].reshape(h, dstride)
+            assert np.array_equal(rows[:, :3 * w].reshape(h, w, 3), F.to_bgr24(fmt, planes)), (rnd, fmt, w, h, pad, off)
+            assert (rows[:, 3 * w:] == 0x5A).all() and (o[:off] == 0x5A).all() and (o[off + h * dstride:] == 0x5A).all(), (rnd, fmt, w, h, pad, off)
