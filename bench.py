@@ -430,9 +430,16 @@ def run_gpu(args):
     pool = ThreadPoolExecutor(min(len(cams), host_threads()))
 
     def submit_all(tick):
-        sel = set(sched[tick % n_pat])
-        list(pool.map(lambda a: path.submit(a[1], a[2], meta, convert=a[0] in sel), zip(range(len(names)), names, host_planes)))
-        return sorted(sel)
+        sel = sorted(sched[tick % n_pat])
+        chosen = set(sel)
+        for c in range(len(names)):
+            if c not in chosen:
+                path.submit(names[c], None, None, convert=False)          # gate-skipped: counted, nothing copied
+        if len(sel) > 1:
+            list(pool.map(lambda c: path.submit(names[c], host_planes[c], meta), sel))   # one producer thread per camera
+        elif sel:
+            path.submit(names[sel[0]], host_planes[sel[0]], meta)
+        return sel
 
     def consume(sel):
         tot = 0

@@ -326,3 +326,98 @@ def test_producers_and_ticker_run_concurrently(path):
             break
     [t.join() for t in th]
     assert not errs and total == n * per and all(v == per - 1 for v in seen.values())
+
+
+# ---- drop-in ReadImage: driven exactly the way reference rtsp_to_rtmp.py:191-251 drives read_image.ReadImage ----
+class _AvPlane:
+    """Stand-in for av.VideoPlane: buffer protocol + line_size/width/height, rows padded like libavcodec's."""
+    def __init__(self, arr, pad=32):
+        self.height, self.width = arr.shape
+        self.line_size = self.width + pad
+        buf = np.full((self.height, self.line_size), 0xEE, np.uint8)
+        buf[:, :self.width] = arr
+        self._b = buf.tobytes()
+
+    def __buffer__(self, flags):
+        return memoryview(self._b)
+
+
+class _AvFormat:
+    def __init__(self, name):
+        self.name = name
+
+
+class _AvPict:
+    def __init__(self, name):
+        self.name = name
+
+
+class _AvFrame:
+    def __init__(self, fmt, planes, pts):
+        self.format, self.planes = _AvFormat(fmt), [_AvPlane(p) for p in planes]
+        self.width, self.height = planes[0].shape[1], planes[0].shape[0]
+        self.pts, self.dts, self.time, self.time_base = pts, pts, pts / 90000, Fraction(1, 90000)
+        self.pict_type = _AvPict("I" if pts % 5 == 0 else "P")
+
+
+class _AvPacket:
+    def __init__(self, idx, fmt, w, h):
+        self.idx, self.is_keyframe, self.is_corrupt = idx, idx % 5 == 0, False
+        self._args = (fmt, w, h)
+
+    def decode(self):
+        fmt, w, h = self._args
+        return [_AvFrame(fmt, make_planes(fmt, w, h, 500 + self.idx), self.idx)]
+
+
+class _RedisKV(FakeRedis):
+    def __init__(self, kv):
+        super().__init__()
+        self.kv = kv
+
+    def get(self, k):
+        return self.kv.get(k)
+
+
+def test_read_image_drop_in_thread():
+    import queue
+    import threading
+    import time as _time
+    from video_edge_ai_proxy_b200 import global_vars
+    from video_edge_ai_proxy_b200.read_image import ReadImage
+    if not torch.cuda.is_available():
+        pytest.fail("marked gpu but no CUDA device")
+    fmt, w, h = "yuvj420p", 640, 480
+    r = _RedisKV({"is_key_frame_only_camA": b"false"})
+    packet_queue, ev, cond = queue.Queue(), threading.Event(), threading.Condition()
+    th = ReadImage(packet_queue=packet_queue, device_id="camA", memory_buffer=3, redis_conn=r,
+                   is_decode_packets_event=ev, lock_condition=cond)          # reference argument names (rtsp_to_rtmp.py:239-244)
+    th.daemon = True
+    th.start()
+    global_vars.query_timestamp = None
+    try:
+        for i in range(10):                                                   # producer side, rtsp_to_rtmp.py:141-160
+            with cond:
+                global_vars.query_timestamp = 1000 + i
+                cond.notify_all()
+            ev.set()
+            packet_queue.put(_AvPacket(i, fmt, w, h))
+            with cond:
+                cond.notify_all()
+            packet_queue.join()
+        deadline = _time.time() + 10
+        while len(r.streams.get("camA", [])) < 3 and _time.time() < deadline:
+            _time.sleep(0.01)
+    finally:
+        th.stop()
+        th.join(timeout=10)
+    msgs = r.streams["camA"]
+    assert len(msgs) == 3                                                     # MAXLEN = memory_buffer
+    VideoFrame, _ = W.dynamic_message_class()
+    for msg, idx in zip(msgs, (7, 8, 9)):
+        vf = VideoFrame(); vf.ParseFromString(msg)
+        assert (vf.width, vf.height, vf.pts, vf.packet, vf.keyframe) == (w, h, idx, idx % 5, idx // 5 + 1)
+        assert vf.frame_type == ("I" if idx % 5 == 0 else "P") and vf.is_keyframe == (idx % 5 == 0)
+        img = np.frombuffer(vf.data, np.uint8).reshape([d.size for d in vf.shape.dim])
+        assert np.array_equal(img, F.to_bgr24(fmt, make_planes(fmt, w, h, 500 + idx)))
+    # a bad frame is dropped with the reference's message and the thread survives (read_image.py:130-131)

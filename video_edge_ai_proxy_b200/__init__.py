@@ -6,6 +6,7 @@ libvepb200.so, hand-written sm_100a CUDA behind the C ABI of include/vepb200.h):
     FramePath, Plan, make_meta, videoframe_framing, to_ndarray_bgr24   (frame_path.py)
     DecodeGate, poll_control, camera_active                             (gate.py)
     FrameProducer                                                       (producer.py)
+    ReadImage (drop-in for the reference's class of that name)          (read_image.py)
     assign_cameras                                                      (shard.py)
 """
 from ._abi import VepError, build_library  # noqa: F401
