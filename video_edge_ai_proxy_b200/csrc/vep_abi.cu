@@ -173,7 +173,7 @@ struct Stream {
     int wr = 0;             // next slot to fill
     int newest = -1;        // newest READY slot
     int n_ready = 0;
-    uint8_t *h_base = nullptr, *d_base = nullptr;
+    uint8_t *h_base = nullptr, *h_in_base = nullptr, *d_base = nullptr;   // pinned out slots, pinned in slots, device slots
     cudaStream_t cs_in = nullptr, cs_out = nullptr;
     cudaEvent_t ev_in = nullptr;
     std::mutex mu;
@@ -341,6 +341,7 @@ static void free_stream(Stream *s) {
     if (s->cs_out) { cudaStreamSynchronize(s->cs_out); cudaStreamDestroy(s->cs_out); }
     if (s->ev_in) cudaEventDestroy(s->ev_in);
     if (s->h_base) cudaFreeHost(s->h_base);
+    if (s->h_in_base) cudaFreeHost(s->h_in_base);
     if (s->d_base) cudaFree(s->d_base);
     delete s;
 }
@@ -565,15 +566,20 @@ extern "C" int vep_stream_open(vep_ctx *c, int stream_id, int fmt, int w, int h,
     s->out_slot = align_up(kHdrRoom + s->out_bytes + kTrailerRoom, 4096);
     const int ns = ring_depth + VEP_MAX_TICKS_IN_FLIGHT + 2;   // ring + ticks in flight + one filling + slack
     s->slots.resize(ns);
-    cudaError_t e = cudaHostAlloc((void **)&s->h_base, (s->in_slot + s->out_slot) * ns, cudaHostAllocDefault);
+    // input staging is written by the CPU (streaming stores) and read by the DMA engine; write-combined pinned
+    // memory (VEP_WC=1) measured the same end to end as ordinary pinned memory on the B200 host, so it stays
+    // opt-in (a caller that reads back a slot obtained from vep_acquire_input would crawl on WC memory)
+    static const bool wc = getenv("VEP_WC") && atoi(getenv("VEP_WC")) == 1;
+    cudaError_t e = cudaHostAlloc((void **)&s->h_base, s->out_slot * ns, cudaHostAllocDefault);
+    if (e == cudaSuccess) e = cudaHostAlloc((void **)&s->h_in_base, s->in_slot * ns, wc ? cudaHostAllocWriteCombined : cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_base, (s->in_slot + s->out_slot) * ns);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->cs_in, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->cs_out, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s->ev_in, cudaEventDisableTiming);
     for (int i = 0; i < ns && e == cudaSuccess; ++i) {
         Slot &sl = s->slots[i];
-        sl.h_in = s->h_base + (s->in_slot + s->out_slot) * i;
-        sl.h_out = sl.h_in + s->in_slot;
+        sl.h_in = s->h_in_base + s->in_slot * i;
+        sl.h_out = s->h_base + s->out_slot * i;
         sl.d_in = s->d_base + (s->in_slot + s->out_slot) * i;
         sl.d_out = sl.d_in + s->in_slot;
         e = cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming);
