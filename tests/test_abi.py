@@ -91,3 +91,12 @@ def test_product_never_imports_the_oracle():
                 text = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
                 assert "swscale_live" not in text and "libyuv2bgr_port" not in text, f
+
+
+def test_missing_library_fails_loudly(monkeypatch):
+    """No silent fallback: without libvepb200.so the binding raises, it does not convert on the CPU."""
+    monkeypatch.setattr(_abi, "_lib", None)
+    monkeypatch.setattr(_abi, "LIB_PATH", os.path.join(ROOT, "video_edge_ai_proxy_b200", "no_such_lib.so"))
+    with pytest.raises(ImportError) as e:
+        _abi.lib()
+    assert "no CPU or PyTorch fallback" in str(e.value)
