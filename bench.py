@@ -427,7 +427,8 @@ def run_gpu(args):
     for name, c in zip(names, cams):
         path.open_stream(name, c["fmt"], c["w"], c["h"], memory_buffer=1)
     meta = make_meta(timestamp=1604660000123, pts=900000, dts=897000, time_base=1 / 90000, is_keyframe=True, frame_type="I", keyframe=1)
-    pool = ThreadPoolExecutor(min(len(cams), host_threads()))
+    # one producer thread per camera like the reference, but never more threads than this rank's share of the host
+    pool = ThreadPoolExecutor(max(1, min(len(cams), host_threads() // max(world, 1))))
 
     def stage_async(tick):
         """Start staging tick `tick`'s frames on the producer threads (one per camera, as in the reference);
@@ -470,10 +471,29 @@ def run_gpu(args):
     torch.cuda.synchronize(dev)
     x1 = time.perf_counter()
     barrier()
+    st_mid = path.stats()
+    # secondary: the decoder writes its planes straight into the pinned staging slot (vep_acquire_input /
+    # vep_commit_input), so no host copy precedes the H2D.  Every slot already holds a valid frame of its camera.
+    z0 = time.perf_counter()
+    pending = []
+    for i in range(e2e_steps):
+        sel = sorted(sched[i % n_pat])
+        for c in sel:
+            path.acquire_raw(names[c]); path.commit_input(names[c], meta)
+        path.tick_begin(); pending.append(sel)
+        if len(pending) == depth:
+            path.tick_wait(); consume(pending.pop(0))
+    while pending:
+        path.tick_wait(); consume(pending.pop(0))
+    torch.cuda.synchronize(dev)
+    z1 = time.perf_counter()
+    barrier()
+    zc_s = max_over_ranks(z1 - z0) if world > 1 else (z1 - z0)
     e2e_s = max_over_ranks(x1 - x0) if world > 1 else (x1 - x0)
     e2e_conv = conv_in(0, e2e_steps)
     e2e_value = (sum_over_ranks(e2e_conv) if world > 1 else e2e_conv) / e2e_s
-    st = path.stats()
+    zc_value = (sum_over_ranks(e2e_conv) if world > 1 else e2e_conv) / zc_s
+    st = st_mid
     h2d_per_step = (st["h2d_bytes"] - base_stats["h2d_bytes"]) // e2e_steps
     d2h_per_step = (st["d2h_bytes"] - base_stats["d2h_bytes"]) // e2e_steps
     pool.shutdown()
@@ -499,7 +519,10 @@ def run_gpu(args):
                                              "frames_per_s": round(total_frames / (strict_ms / 1e3), 1)}, "kernel": {"persistent": "vep::yuv_to_bgr24_persistent", "oneshot": "vep::yuv_to_bgr24_batched"}.get(os.environ.get("VEP_KERNEL", "tick"), "vep::yuv_to_bgr24_tick")},
         "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d_per_step), "d2h_bytes_per_step": int(d2h_per_step),
                 "steps": e2e_steps, "api": "FramePath.submit from one producer thread per camera (host planes -> pinned staging) + tick_begin/tick_wait (3 ticks in flight) + result_packed",
-                "pcie_gbs": round((h2d_per_step + d2h_per_step) * e2e_steps / e2e_s / 1e9, 2), "message_bytes": msg_bytes},
+                "pcie_gbs": round((h2d_per_step + d2h_per_step) * e2e_steps / e2e_s / 1e9, 2), "message_bytes": msg_bytes,
+                "producer_threads": pool._max_workers,
+                "decoder_writes_into_pinned_slot": {"value": round(zc_value, 1), "unit": UNIT,
+                                                    "api": "vep_acquire_input/vep_commit_input instead of vep_submit: no host staging copy before the H2D"}},
         "gpu_launches": gpu_launches,
         "clocks": clocks,
     }

@@ -207,6 +207,13 @@ class FramePath:
             out.append(np.frombuffer(buf, np.uint8).reshape(shp[0], strides[i])[:, :shp[1]])
         return out
 
+    def acquire_raw(self, device_id: str):
+        """(pointers, strides) of the next pinned staging slot as ctypes arrays — for producers that hand the
+        addresses to native code (a decoder's get_buffer callback) instead of numpy."""
+        ptrs, strides = (C.c_void_p * 3)(), (C.c_int32 * 3)()
+        check(self._L.vep_acquire_input(self._ctx, self._sid(device_id), C.byref(ptrs), C.byref(strides)), "vep_acquire_input")
+        return ptrs, strides
+
     def commit_input(self, device_id: str, meta: Optional[FrameMeta] = None):
         check(self._L.vep_commit_input(self._ctx, self._sid(device_id),
                                        C.byref(meta) if meta is not None else None), "vep_commit_input")
