@@ -722,6 +722,8 @@ static void write_framing(Stream *s, Slot &sl) {
     sl.msg_len = (size_t)pl + s->out_bytes + sl_len;
 }
 
+static int tick_enqueue(vep_ctx *c, TickRec &t, int *n_frames);
+
 extern "C" int vep_tick_begin(vep_ctx *c, int *n_frames) {
     if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
     if (n_frames) *n_frames = 0;
@@ -730,6 +732,22 @@ extern "C" int vep_tick_begin(vep_ctx *c, int *n_frames) {
     if (c->ticks_in_flight >= VEP_MAX_TICKS_IN_FLIGHT) return fail(VEP_ERR_BUSY, "%d ticks already in flight; call vep_tick_wait", VEP_MAX_TICKS_IN_FLIGHT);
     TickRec &t = c->ticks[(c->tick_head + c->ticks_in_flight) % VEP_MAX_TICKS_IN_FLIGHT];
     t.slots.clear();
+    const int rc = tick_enqueue(c, t, n_frames);
+    if (rc != VEP_OK) {
+        // a CUDA call failed half-way: the frames of this tick are dropped (the reference drops a frame on any
+        // exception, read_image.py:130-131) and their slots are released so the cameras are not wedged
+        for (auto &r : t.slots) {
+            cudaStreamSynchronize(r.s->cs_in);
+            cudaStreamSynchronize(r.s->cs_out);
+            std::lock_guard<std::mutex> sl_lk(r.s->mu);
+            r.s->slots[r.slot].state = SLOT_FREE;
+        }
+        t.slots.clear();
+    }
+    return rc;
+}
+
+static int tick_enqueue(vep_ctx *c, TickRec &t, int *n_frames) {
     std::vector<vep_frame_desc> descs;
     std::vector<Stream *> involved;
     // 1. H2D of every committed frame on its camera's input stream
