@@ -193,6 +193,7 @@ struct vep_ctx {
                                  // (VEP_KERNEL=oneshot; also the fallback beyond 128 frames); 0: VEP_KERNEL=persistent
     int rpt = 2, minb = 4;       // tick kernel variant: row pairs per lane, min CTAs/SM (VEP_RPT, VEP_MINB)
     int pdl = 1;                 // programmatic dependent launch attribute on tick launches (VEP_PDL=0 disables)
+    int specialize = 1;          // use the per-format instantiation for single-format launches (VEP_SPECIALIZE=0 disables)
     int store_mode = 0;          // one-shot kernel only (VEP_STORE_MODE)
     int resident_warps = 0;      // persistent kernel: warps the whole GPU keeps resident
     cudaStream_t main = nullptr;
@@ -243,6 +244,9 @@ static void fill_tick(const Tables &t, std::vector<uint8_t> &blob) {
     int per = n ? t.tick_cta_begin[1] - t.tick_cta_begin[0] : 0;
     for (int i = 1; i < n && per > 0; ++i) if (t.tick_cta_begin[i + 1] - t.tick_cta_begin[i] != per) per = 0;
     P->uniform_ctas = (n > 0 && n <= 65535) ? per : 0;
+    int only = n ? t.frames[0].fmt : -1;
+    for (int i = 1; i < n; ++i) if (t.frames[i].fmt != only) only = -1;
+    P->only_fmt = only;        // host-side hint: all frames share one pixel format -> format-specialised kernel
     for (int i = 0; i <= n; ++i) P->cta_begin[i] = t.tick_cta_begin[i];
     for (int i = 0; i < n; ++i) P->frames[i] = t.frames[i];
 }
@@ -255,7 +259,18 @@ static int make_tick_blob(const Tables &t, std::vector<uint8_t> &blob, int *grid
     return 0;
 }
 template <int NF>
-static const void *tick_kernel(int rpt, int minb) {
+static const void *tick_kernel(int rpt, int minb, int only_fmt) {
+    if (rpt == 2 && minb == 4) {   // the default variant also exists specialised per pixel format
+        switch (only_fmt) {
+            case VEP_FMT_YUV420P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_YUV420P>;
+            case VEP_FMT_YUVJ420P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_YUVJ420P>;
+            case VEP_FMT_NV12: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_NV12>;
+            case VEP_FMT_NV21: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_NV21>;
+            case VEP_FMT_YUV422P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_YUV422P>;
+            case VEP_FMT_YUVJ422P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_YUVJ422P>;
+            default: break;
+        }
+    }
     if (rpt == 2) return minb >= 4 ? (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4> : (const void *)vep::yuv_to_bgr24_tick<NF, 2, 3>;
     if (minb >= 8) return (const void *)vep::yuv_to_bgr24_tick<NF, 1, 8>;
     if (minb >= 6) return (const void *)vep::yuv_to_bgr24_tick<NF, 1, 6>;
@@ -263,7 +278,9 @@ static const void *tick_kernel(int rpt, int minb) {
 }
 static int launch_tick(const vep_ctx *c, int cap, const std::vector<uint8_t> &blob, int grid, cudaStream_t st) {
     if (grid <= 0) return VEP_OK;
-    const void *fn = cap == kTickCapSmall ? tick_kernel<kTickCapSmall>(c->rpt, c->minb) : tick_kernel<kTickCapLarge>(c->rpt, c->minb);
+    const int32_t *hdr0 = reinterpret_cast<const int32_t *>(blob.data());   // n_frames, wait_prior, uniform_ctas, only_fmt
+    const int only = c->specialize ? hdr0[3] : -1;
+    const void *fn = cap == kTickCapSmall ? tick_kernel<kTickCapSmall>(c->rpt, c->minb, only) : tick_kernel<kTickCapLarge>(c->rpt, c->minb, only);
     void *args[1] = {const_cast<uint8_t *>(blob.data())};
     cudaLaunchConfig_t cfg{};
     const int32_t *hdr = reinterpret_cast<const int32_t *>(blob.data());   // n_frames, wait_prior, uniform_ctas
@@ -317,6 +334,8 @@ extern "C" int vep_create(int device, vep_ctx **out) {
     const char *er = getenv("VEP_RPT"), *em = getenv("VEP_MINB");
     c->rpt = (er && atoi(er) == 1) ? 1 : 2;
     c->minb = em ? atoi(em) : (c->rpt == 2 ? 4 : 6);
+    const char *es = getenv("VEP_SPECIALIZE");
+    c->specialize = (es && atoi(es) == 0) ? 0 : 1;
     const char *ep = getenv("VEP_PDL");
     c->pdl = (ep && atoi(ep) == 0) ? 0 : 1;
     CUDA_TRY(cudaFuncSetAttribute(vep::yuv_to_bgr24_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, vep::kPSmemBytes));

@@ -397,12 +397,14 @@ struct TickParams {
                              // 0: the caller declared this launch independent of the previous kernel
     int32_t uniform_ctas;    // > 0: every frame has this many CTAs and the grid is (uniform_ctas, n_frames):
                              //      blockIdx.y is the frame, no search (homogeneous camera fleets)
-    int32_t pad_;
+    int32_t only_fmt;        // host-side only: the single pixel format of the launch, or -1 (selects the instantiation)
     int32_t cta_begin[(NF + 1 + 3) / 4 * 4];   // cta_begin[f] = first CTA of frame f; [n_frames] = grid size
     FrameDev frames[NF];
 };
 
-template <int NF, int RPT, int MINB>
+// ONLY >= 0: every frame of the launch has pixel format ONLY (a homogeneous fleet, the common case) and the other
+// formats' code is compiled out: a third of the instruction footprint, fewer instruction-cache misses.
+template <int NF, int RPT, int MINB, int ONLY = -1>
 __global__ void __launch_bounds__(kThreads, MINB)
 yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     __shared__ __align__(128) uint8_t tile[kWarpsPerCta][2][kSegBytes];
@@ -421,6 +423,7 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
         fi = lo;
     }
     const FrameDev &f = p.frames[fi];
+    const int fmt = ONLY >= 0 ? ONLY : f.fmt;
     const int first = (cta - p.cta_begin[fi]) * (f.fast == PATH_GENERIC ? kGenericBlocksPerCta : kWarpsPerCta);
 
     if (f.fast == PATH_GENERIC) {
@@ -446,8 +449,8 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     // ---- all loads first ----
     uint4 ya[RPT], yb[RPT], ca[RPT];   // ca: planar {U.lo,U.hi,V.lo,V.hi}; nv12: the 16 interleaved chroma bytes
     uint4 pu = make_uint4(0, 0, 0, 0);
-    const bool nv12 = fmt_is_semiplanar(f.fmt);
-    const int cshift = fmt_is_422(f.fmt) ? 1 : 0;           // 4:2:2: chroma row of luma row j is row j, not j/2
+    const bool nv12 = fmt_is_semiplanar(fmt);
+    const int cshift = fmt_is_422(fmt) ? 1 : 0;           // 4:2:2: chroma row of luma row j is row j, not j/2
     if (active) {
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
@@ -463,7 +466,7 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
             }
         }
         if (nv12) pu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)(rp0 > 0 ? rp0 - 1 : 0) * f.sc0 + x));
-        if (f.fmt == FMT_NV21) {                            // V first: swap each pair once, then it is NV12
+        if (fmt == FMT_NV21) {                            // V first: swap each pair once, then it is NV12
             pu = swap_pairs(pu);
 #pragma unroll
             for (int r = 0; r < RPT; ++r) ca[r] = swap_pairs(ca[r]);
@@ -478,20 +481,20 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
             // 4:2:2: the odd luma row has a chroma row of its own.  One row at a time (park it, then the next)
             // keeps this secondary format from raising the register count of the 4:2:0 path.
             uint32_t o[12];
-            if (f.fmt == FMT_YUV422P) compute_planar_row<false>(ya[r], make_uint2(ca[r].x, ca[r].y), make_uint2(ca[r].z, ca[r].w), o);
+            if (fmt == FMT_YUV422P) compute_planar_row<false>(ya[r], make_uint2(ca[r].x, ca[r].y), make_uint2(ca[r].z, ca[r].w), o);
             else compute_planar_row<true>(ya[r], make_uint2(ca[r].x, ca[r].y), make_uint2(ca[r].z, ca[r].w), o);
 #pragma unroll
             for (int k = 0; k < 3; ++k) *reinterpret_cast<uint4 *>(t0 + lane * 48 + k * 16) = make_uint4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
             const uint2 ub = ld_stream_v2(f.c0 + (size_t)(2 * rp + 1) * f.sc0 + (x >> 1));
             const uint2 vb = ld_stream_v2(f.c1 + (size_t)(2 * rp + 1) * f.sc1 + (x >> 1));
-            if (f.fmt == FMT_YUV422P) compute_planar_row<false>(yb[r], ub, vb, o);
+            if (fmt == FMT_YUV422P) compute_planar_row<false>(yb[r], ub, vb, o);
             else compute_planar_row<true>(yb[r], ub, vb, o);
 #pragma unroll
             for (int k = 0; k < 3; ++k) *reinterpret_cast<uint4 *>(t1 + lane * 48 + k * 16) = make_uint4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
         } else if (active) {
             uint32_t o0[12], o1[12];
-            if (f.fmt == FMT_YUV420P) compute_planar<false>(ya[r], yb[r], make_uint2(ca[r].x, ca[r].y), make_uint2(ca[r].z, ca[r].w), o0, o1);
-            else if (f.fmt == FMT_YUVJ420P) compute_planar<true>(ya[r], yb[r], make_uint2(ca[r].x, ca[r].y), make_uint2(ca[r].z, ca[r].w), o0, o1);
+            if (fmt == FMT_YUV420P) compute_planar<false>(ya[r], yb[r], make_uint2(ca[r].x, ca[r].y), make_uint2(ca[r].z, ca[r].w), o0, o1);
+            else if (fmt == FMT_YUVJ420P) compute_planar<true>(ya[r], yb[r], make_uint2(ca[r].x, ca[r].y), make_uint2(ca[r].z, ca[r].w), o0, o1);
             else compute_nv12(ya[r], yb[r], ca[r], r == 0 ? pu : ca[r > 0 ? r - 1 : 0], rp == hp - 1, o0, o1);
 #pragma unroll
             for (int k = 0; k < 3; ++k) {   // 48 B lane stride: conflict-free per quarter warp
