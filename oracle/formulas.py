@@ -208,7 +208,49 @@ def nv21_to_bgr24(Y, VU) -> np.ndarray:
     return nv12_to_bgr24(Y, UV)
 
 
+def yuv420p10_to_bgr24(Y, U, V) -> np.ndarray:
+    """yuv420p10le (10-bit samples, limited range) -> BGR24.  Probed against the live library, exact for H >= 8
+    on uniform and extreme sample values: libswscale sends 10-bit input through its generic vertical scaler (15-bit
+    intermediates = sample << 5), so the rule is formula C's with 11-bit terms: odd rows use chroma row k
+    (`(u << 1) - 1024`), even rows the sum with the row above (`(u_up + u) - 1024`), luma `(Y << 1)`; rows H-2 and
+    H-1 drop to the plain-C stage on 8-bit values y = (Y + 2) >> 2, u = min((blend + 8192) >> 14, 255)."""
+    h, w = Y.shape
+    if h < 8:
+        raise ValueError("yuv420p10le restatement covers H >= 8 only")
+    hc = h // 2
+    Yi, Ui, Vi = Y.astype(np.int32), U.astype(np.int32), V.astype(np.int32)
+    k = coeffs_simd(False)
+    rep = lambda a: np.repeat(a, 2, axis=1)[:, :w]
+    out = np.empty((h, w, 3), np.uint8)
+
+    def stage(Yr, Uw, Vw):
+        y = (((Yr << 1) - k["yOff"]) * k["yC"]) >> 16
+        cb = (Uw * k["ub"]) >> 16
+        cr = (Vw * k["vr"]) >> 16
+        cg = ((Uw * k["ug"]) >> 16) + ((Vw * k["vg"]) >> 16)
+        return np.stack([_sat_u8(y + cb), _sat_u8(y + cg), _sat_u8(y + cr)], -1)
+
+    up = np.maximum(np.arange(hc) - 1, 0)
+    out[1::2] = stage(Yi[1::2], rep((Ui << 1) - 1024), rep((Vi << 1) - 1024))
+    out[0::2] = stage(Yi[0::2], rep((Ui[up] + Ui) - 1024), rep((Vi[up] + Vi) - 1024))
+    c = _coeffs_c_path(False)
+    for j in (h - 2, h - 1):
+        kr = j >> 1
+        if j & 1:
+            k0, k1, a = kr, min(kr + 1, hc - 1), 1024
+        else:
+            k0, k1, a = kr - 1, kr, 3072
+        if k0 == k1:
+            a = 0
+        u = np.minimum((Ui[k0] * (4096 - a) + Ui[k1] * a + 8192) >> 14, 255)   # the C tables clip the chroma index to 8 bits
+        v = np.minimum((Vi[k0] * (4096 - a) + Vi[k1] * a + 8192) >> 14, 255)
+        out[j] = _c_path_pixels((Yi[j] + 2) >> 2, np.repeat(u, 2)[:w], np.repeat(v, 2)[:w], c)
+    return out
+
+
 def to_bgr24(fmt: str, planes) -> np.ndarray:
+    if fmt == "yuv420p10le":
+        return yuv420p10_to_bgr24(planes[0], planes[1], planes[2])
     if fmt == "yuv422p":
         return yuv422p_to_bgr24(planes[0], planes[1], planes[2], False)
     if fmt == "yuvj422p":

@@ -127,3 +127,69 @@ int port_nv12_to_bgr24(const uint8_t *Y, int sy, const uint8_t *UV, int suv, int
     }
     return 0;
 }
+
+/* yuv420p10le (oracle/formulas.py: yuv420p10_to_bgr24).  Planes hold little-endian 16-bit samples <= 1023;
+ * strides in bytes.  H >= 8. */
+static void row_simd11(const uint16_t *y, const int *Uw, const int *Vw, uint8_t *dst, int w)
+{
+    const simd_k *k = &K_LIMITED;
+    for (int x = 0; x < w; x++) {
+        int uw = Uw[x >> 1], vw = Vw[x >> 1];
+        int cb = asr16(uw * k->ub), cr = asr16(vw * k->vr);
+        int cg = asr16(uw * k->ug) + asr16(vw * k->vg);
+        int yy = asr16((((int)y[x] << 1) - k->yOff) * k->yC);
+        dst[3 * x + 0] = sat_u8(yy + cb);
+        dst[3 * x + 1] = sat_u8(yy + cg);
+        dst[3 * x + 2] = sat_u8(yy + cr);
+    }
+}
+
+int port_yuv420p10_to_bgr24(const uint8_t *Y, int sy, const uint8_t *U, int su, const uint8_t *V, int sv,
+                            int w, int h, uint8_t *dst, int sd)
+{
+    if (w <= 0 || h < 8 || (w & 1) || (h & 1) || w > MAXW) return -1;
+    int a0[MAXW / 2], a1[MAXW / 2];
+    uint8_t y8[MAXW];
+    const int hc = h / 2;
+    for (int j = 0; j < h; j++) {
+        const int k = j >> 1;
+        const uint16_t *y = (const uint16_t *)(Y + (size_t)j * sy);
+        uint8_t *d = dst + (size_t)j * sd;
+        if (j < h - 2) {
+            const uint16_t *cu = (const uint16_t *)(U + (size_t)k * su), *cv = (const uint16_t *)(V + (size_t)k * sv);
+            const uint16_t *pu = (const uint16_t *)(U + (size_t)(k > 0 ? k - 1 : 0) * su), *pv = (const uint16_t *)(V + (size_t)(k > 0 ? k - 1 : 0) * sv);
+            for (int i = 0; i < w / 2; i++) {
+                if (j & 1) { a0[i] = (cu[i] << 1) - 1024; a1[i] = (cv[i] << 1) - 1024; }
+                else       { a0[i] = pu[i] + cu[i] - 1024; a1[i] = pv[i] + cv[i] - 1024; }
+            }
+            row_simd11(y, a0, a1, d, w);
+        } else {
+            int k0, k1, a;
+            if (j & 1) { k0 = k; k1 = k + 1 < hc ? k + 1 : hc - 1; a = 1024; }
+            else       { k0 = k - 1; k1 = k; a = 3072; }
+            if (k0 == k1) a = 0;
+            const uint16_t *u0 = (const uint16_t *)(U + (size_t)k0 * su), *u1 = (const uint16_t *)(U + (size_t)k1 * su);
+            const uint16_t *v0 = (const uint16_t *)(V + (size_t)k0 * sv), *v1 = (const uint16_t *)(V + (size_t)k1 * sv);
+            for (int i = 0; i < w / 2; i++) {
+                a0[i] = (u0[i] * (4096 - a) + u1[i] * a + 8192) >> 14; if (a0[i] > 255) a0[i] = 255;
+                a1[i] = (v0[i] * (4096 - a) + v1[i] * a + 8192) >> 14; if (a1[i] > 255) a1[i] = 255;
+            }
+            /* formula B takes 8-bit luma; (Y+2)>>2 can reach 256, which row_cpath's closed form handles */
+            {
+                const int base = -(384 << 16) - C_OY + 326 * C_CY + 0x8000;
+                (void)y8;
+                for (int x = 0; x < w; x++) {
+                    int uu = a0[x >> 1], vv = a1[x >> 1];
+                    int dr = asr16(vv * C_CRV) - (C_CRV >> 9);
+                    int db = asr16(uu * C_CBU) - (C_CBU >> 9);
+                    int dg = asr16(uu * C_CGU) - (-((-C_CGU + 511) >> 9)) + asr16(vv * C_CGV) - (-((-C_CGV + 511) >> 9));
+                    int Yv = (y[x] + 2) >> 2;
+                    d[3 * x + 0] = sat_u8(asr16(base + (Yv + db) * C_CY));
+                    d[3 * x + 1] = sat_u8(asr16(base + (Yv + dg) * C_CY));
+                    d[3 * x + 2] = sat_u8(asr16(base + (Yv + dr) * C_CY));
+                }
+            }
+        }
+    }
+    return 0;
+}

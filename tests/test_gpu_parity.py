@@ -62,7 +62,8 @@ def test_exhaustive_yuv_triples_planar_both_ranges(path):
             assert np.array_equal(got[r0:r0 + 512], want), (fmt, r0)
 
 
-ALL_FORMATS = ["yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p"]
+ALL_FORMATS = ["yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le"]
+TALL_ONLY = ("nv12", "nv21", "yuv420p10le")     # formats whose rule needs H >= 8
 
 
 @pytest.mark.parametrize("fmt", ALL_FORMATS)
@@ -77,13 +78,13 @@ def test_seeded_random_config_sizes(path, fmt):
 def test_ragged_geometries_take_the_generic_path(path, fmt):
     for w in (2, 6, 14, 18, 30, 34, 62, 130, 510, 514, 642, 1922):
         for h in (2, 4, 8, 10, 18, 50):
-            if fmt in ("nv12", "nv21") and h < 8:
+            if fmt in TALL_ONLY and h < 8:
                 continue
             planes = make_planes(fmt, w, h, 31 * w + h)
             assert np.array_equal(gpu_convert(path, fmt, planes), F.to_bgr24(fmt, planes)), (fmt, w, h)
 
 
-@pytest.mark.parametrize("fmt", ["yuv420p", "nv12", "nv21", "yuvj422p"])
+@pytest.mark.parametrize("fmt", ["yuv420p", "nv12", "nv21", "yuvj422p", "yuv420p10le"])
 def test_fast_path_widths_and_partial_segments(path, fmt):
     # multiples of 16 around the 512-px segment boundary: full, partial and single-lane segments
     for w in (16, 32, 496, 512, 528, 1008, 1024, 1040, 2048, 4096):
@@ -96,7 +97,8 @@ def test_live_libswscale_agrees_on_the_box(path):
         pytest.skip("bundled libswscale not found")
     assert L.on_simd_path()
     for fmt, w, h in (("yuv420p", 1920, 1080), ("yuvj420p", 640, 480), ("nv12", 1280, 720), ("yuv420p", 50, 6),
-                      ("nv21", 1920, 1080), ("yuv422p", 1280, 720), ("yuvj422p", 1920, 1080), ("yuvj422p", 50, 6)):
+                      ("nv21", 1920, 1080), ("yuv422p", 1280, 720), ("yuvj422p", 1920, 1080), ("yuvj422p", 50, 6),
+                      ("yuv420p10le", 1920, 1080), ("yuv420p10le", 50, 10)):
         planes = make_planes(fmt, w, h, 77)
         assert np.array_equal(gpu_convert(path, fmt, planes), L.to_bgr24(fmt, planes, w, h)), (fmt, w, h)
 
@@ -193,7 +195,7 @@ def test_persistent_tma_kernel_bit_identical(golden_pixels, small_frames):
                 assert np.array_equal(gpu_convert(p, fmt, planes), want), (fmt, w, h)
             for fmt, w, h in (("yuv420p", 16, 8), ("yuv420p", 48, 8), ("nv12", 528, 16), ("yuvj420p", 1040, 8), ("nv12", 32, 8),
                               ("yuv420p", 64, 8), ("yuv420p", 496, 4), ("nv12", 18, 10), ("nv21", 1280, 720), ("nv21", 48, 8),
-                              ("yuvj422p", 640, 480), ("yuv422p", 50, 6)):
+                              ("yuvj422p", 640, 480), ("yuv422p", 50, 6), ("yuv420p10le", 640, 480), ("yuv420p10le", 50, 10)):
                 planes = make_planes(fmt, w, h, w + h)
                 assert np.array_equal(gpu_convert(p, fmt, planes), F.to_bgr24(fmt, planes)), (fmt, w, h)
             # a mixed batch in one launch: bulk, vector and generic frames together
@@ -239,7 +241,8 @@ def test_tick_kernel_variants_bit_identical(env, small_frames):
             assert np.array_equal(gpu_convert(p, fmt, planes), want), (env, fmt, w, h)
         for fmt, w, h in (("yuv420p", 1920, 1080), ("nv12", 1920, 1080), ("yuvj420p", 640, 480), ("yuv420p", 528, 6), ("nv12", 1040, 10),
                           ("yuv420p", 16, 2), ("nv12", 3840, 2160), ("yuv420p", 642, 482), ("nv12", 64, 14),
-                          ("nv21", 1280, 720), ("yuvj422p", 1280, 720), ("yuv422p", 528, 6), ("nv21", 38, 12), ("yuvj422p", 50, 6)):
+                          ("nv21", 1280, 720), ("yuvj422p", 1280, 720), ("yuv422p", 528, 6), ("nv21", 38, 12), ("yuvj422p", 50, 6),
+                          ("yuv420p10le", 1280, 720), ("yuv420p10le", 528, 10), ("yuv420p10le", 38, 12)):
             planes = make_planes(fmt, w, h, w + h)
             assert np.array_equal(gpu_convert(p, fmt, planes), F.to_bgr24(fmt, planes)), (env, fmt, w, h)
         # 40 frames in one launch (128-entry parameter table) and 150 frames (falls back to the device table)
@@ -247,7 +250,7 @@ def test_tick_kernel_variants_bit_identical(env, small_frames):
             descs, keep = [], []
             for i in range(n):
                 fmt, w, h = (("yuv420p", 320, 240), ("nv12", 352, 288), ("yuvj420p", 160, 120), ("yuv420p", 50, 6),
-                             ("yuvj422p", 320, 240), ("nv21", 64, 48))[i % 6]
+                             ("yuvj422p", 320, 240), ("nv21", 64, 48), ("yuv420p10le", 160, 120))[i % 7]
                 planes = make_planes(fmt, w, h, i)
                 t = [torch.from_numpy(q).cuda() for q in planes]
                 out = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
@@ -355,13 +358,16 @@ def test_random_geometry_fuzz_one_launch_per_round(path):
             fmt = ALL_FORMATS[int(rng.integers(len(ALL_FORMATS)))]
             w = int(widths[int(rng.integers(len(widths)))])
             h = int(rng.choice([2, 4, 6, 8, 10, 12, 18, 34, 50]))
-            if fmt in ("nv12", "nv21"):
+            if fmt in TALL_ONLY:
                 h = max(h, 8)
             pad = int(rng.choice([0, 0, 16, 32, 7, 48]))
             off = int(rng.choice([0, 0, 16, 8, 3]))
+            if fmt == "yuv420p10le":                      # 16-bit samples: planes and strides stay 2-byte aligned
+                pad, off = pad & ~1, off & ~1
             planes = make_planes(fmt, w, h, 1000 * rnd + i)
             bufs, ptrs, strides = [], [], []
             for p in planes:
+                p = np.ascontiguousarray(p).view(np.uint8).reshape(p.shape[0], -1)     # rows as bytes
                 ph, pw = p.shape
                 buf = torch.full((ph * (pw + pad) + off + 64,), 0x33, dtype=torch.uint8, device="cuda")
                 view = buf[off:off + ph * (pw + pad)].view(ph, pw + pad)

@@ -41,7 +41,7 @@ def test_small_fixtures_numpy_and_c_port(small_frames):
         assert np.array_equal(P.to_bgr24(fmt, planes), out), (fmt, w, h)
 
 
-@pytest.mark.parametrize("row", range(30))
+@pytest.mark.parametrize("row", range(34))
 def test_numpy_restatement_matches_golden_table(golden_pixels, row):
     rows = golden_pixels["rows"]
     if row >= len(rows):
@@ -55,6 +55,19 @@ def test_numpy_restatement_matches_golden_table(golden_pixels, row):
     else:
         out = F.to_bgr24(r["fmt"], planes)
     assert _digest(out) == (r["sum"], r["sha256"]), r
+
+
+def test_ten_bit_extreme_samples_against_live_library():
+    if not L.available():
+        pytest.skip("bundled libswscale not found")
+    rng = np.random.default_rng(11)
+    for w, h in ((64, 8), (130, 18), (640, 480)):
+        Y = rng.choice(np.array([0, 1, 2, 3, 64, 940, 1020, 1021, 1022, 1023], np.uint16), (h, w))
+        U = rng.choice(np.array([0, 1, 512, 1022, 1023], np.uint16), (h // 2, w // 2))
+        V = rng.choice(np.array([0, 3, 512, 1020, 1023], np.uint16), (h // 2, w // 2))
+        assert np.array_equal(L.to_bgr24("yuv420p10le", (Y, U, V), w, h), F.to_bgr24("yuv420p10le", (Y, U, V))), (w, h)
+    with pytest.raises(ValueError):
+        F.to_bgr24("yuv420p10le", make_planes("yuv420p10le", 16, 6, 0))
 
 
 def test_c_port_matches_numpy_at_config_sizes():
@@ -107,10 +120,10 @@ def test_live_library_reproduces_survey_checksums(golden_pixels, fmt, w, h, seed
 
 @needs_live
 def test_live_vs_restatement_ragged_widths_and_heights():
-    for fmt in ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p"):
+    for fmt in ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le"):
         for w in (2, 6, 14, 16, 18, 30, 34, 62, 130, 642):
             for h in (2, 4, 8, 10, 18):
-                if fmt in ("nv12", "nv21") and h < 8:
+                if fmt in ("nv12", "nv21", "yuv420p10le") and h < 8:
                     continue
                 planes = make_planes(fmt, w, h, 1000 * w + h)
                 assert np.array_equal(L.to_bgr24(fmt, planes, w, h), F.to_bgr24(fmt, planes)), (fmt, w, h)

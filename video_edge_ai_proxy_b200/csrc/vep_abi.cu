@@ -93,26 +93,30 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1) 
     for (int i = 0; i < n; ++i) {
         const vep_frame_desc &s = d[i];
         if (!s.convert) continue;
-        if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_YUVJ422P) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
+        if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_YUV420P10LE) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
         const int w = s.width, h = s.height;
         if (w <= 0 || h <= 0 || w > kMaxDim || h > kMaxDim || (w & 1) || (h & 1))
             return fail(VEP_ERR_GEOMETRY, "desc %d: %dx%d — 4:2:0 needs even, positive dimensions <= %d", i, w, h, kMaxDim);
         const bool nv12 = vep::fmt_is_semiplanar(s.fmt);
-        if (nv12 && h < 8) return fail(VEP_ERR_GEOMETRY, "desc %d: nv12 height %d < 8 (swscale changes its vertical chroma filter there)", i, h);
+        const int bps = vep::fmt_bytes_per_sample(s.fmt);
+        if ((nv12 || bps == 2) && h < 8) return fail(VEP_ERR_GEOMETRY, "desc %d: nv12/nv21/10-bit height %d < 8 (swscale changes its vertical chroma filter there)", i, h);
         if (!s.plane[0] || !s.plane[1] || (!nv12 && !s.plane[2]) || !s.dst) return fail(VEP_ERR_INVALID_ARG, "desc %d: null plane or dst", i);
-        const int cw = nv12 ? w : w / 2;
-        if (s.stride[0] < w || s.stride[1] < cw || (!nv12 && s.stride[2] < cw) || s.dst_stride < 3 * w)
+        const int cw = (nv12 ? w : w / 2) * bps;
+        if (s.stride[0] < w * bps || s.stride[1] < cw || (!nv12 && s.stride[2] < cw) || s.dst_stride < 3 * w)
             return fail(VEP_ERR_GEOMETRY, "desc %d: a stride is smaller than its row", i);
+        if (bps == 2 && ((s.stride[0] | s.stride[1] | s.stride[2]) & 1 || !aligned(s.plane[0], 2) || !aligned(s.plane[1], 2) || !aligned(s.plane[2], 2)))
+            return fail(VEP_ERR_GEOMETRY, "desc %d: 16-bit samples need 2-byte aligned planes and even strides", i);
         FrameDev f{};
         f.y = s.plane[0]; f.c0 = s.plane[1]; f.c1 = nv12 ? nullptr : s.plane[2]; f.dst = s.dst;
         f.sy = s.stride[0]; f.sc0 = s.stride[1]; f.sc1 = nv12 ? 0 : s.stride[2]; f.sd = s.dst_stride;
         f.w = w; f.h = h; f.fmt = s.fmt;
-        const size_t ca = nv12 ? 16 : 8;
+        const size_t ca = (nv12 || bps == 2) ? 16 : 8;
         const bool vec = (w % 16 == 0) && aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
-                         (nv12 || (aligned(f.c1, 8) && f.sc1 % 8 == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
-        const bool bulk = vec && (w % 32 == 0) && aligned(f.c0, 16) && f.sc0 % 16 == 0 && (nv12 || (aligned(f.c1, 16) && f.sc1 % 16 == 0));
+                         (nv12 || (aligned(f.c1, ca) && f.sc1 % ca == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
+        const bool bulk = vec && bps == 1 && (w % 32 == 0) && aligned(f.c0, 16) && f.sc0 % 16 == 0 && (nv12 || (aligned(f.c1, 16) && f.sc1 % 16 == 0));
         f.fast = bulk ? vep::PATH_BULK : vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;
-        f.fast_tbl = vep::fmt_is_422(s.fmt) ? vep::PATH_GENERIC : f.fast;   // only the tick kernel has a vector path for 4:2:2
+        // only the tick kernel has a vector path for 4:2:2 and for 10-bit samples
+        f.fast_tbl = (vep::fmt_is_422(s.fmt) || bps == 2) ? vep::PATH_GENERIC : f.fast;
         f.segs = (w + vep::kSegPx - 1) / vep::kSegPx;
         f.segs_magic = f.segs == 1 ? 0u : (uint32_t)((((uint64_t)1 << 32) + f.segs - 1) / f.segs);
         f.item_begin = t.total_items;
@@ -132,7 +136,7 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1) 
         }
         if ((int64_t)t.total_items + items > (int64_t)1 << 30) return fail(VEP_ERR_INVALID_ARG, "batch too large");
         t.total_items += items;
-        t.alg_bytes += vep::fmt_is_422(s.fmt) ? (int64_t)w * h * 5 : (int64_t)w * h * 9 / 2;   // 4:2:2 reads 2 B/px
+        t.alg_bytes += vep::fmt_is_422(s.fmt) ? (int64_t)w * h * 5 : bps == 2 ? (int64_t)w * h * 6 : (int64_t)w * h * 9 / 2;   // 4:2:2 reads 2 B/px, 10-bit 3 B/px
         t.n_converted++;
     }
     FrameDev sentinel{};
@@ -268,6 +272,7 @@ static const void *tick_kernel(int rpt, int minb, int only_fmt) {
             case VEP_FMT_NV21: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_NV21>;
             case VEP_FMT_YUV422P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_YUV422P>;
             case VEP_FMT_YUVJ422P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_YUVJ422P>;
+            case VEP_FMT_YUV420P10LE: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 3, vep::FMT_YUV420P10>;   // 80 registers: no spills
             default: break;
         }
     }
@@ -562,9 +567,9 @@ static Stream *find_stream(vep_ctx *c, int id) {
 
 extern "C" int vep_stream_open(vep_ctx *c, int stream_id, int fmt, int w, int h, int ring_depth) {
     if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
-    if (fmt < VEP_FMT_YUV420P || fmt > VEP_FMT_YUVJ422P) return fail(VEP_ERR_INVALID_ARG, "unknown fmt %d", fmt);
+    if (fmt < VEP_FMT_YUV420P || fmt > VEP_FMT_YUV420P10LE) return fail(VEP_ERR_INVALID_ARG, "unknown fmt %d", fmt);
     if (w <= 0 || h <= 0 || w > kMaxDim || h > kMaxDim || (w & 1) || (h & 1)) return fail(VEP_ERR_GEOMETRY, "%dx%d: need even, positive dimensions", w, h);
-    if (vep::fmt_is_semiplanar(fmt) && h < 8) return fail(VEP_ERR_GEOMETRY, "nv12/nv21 height %d < 8", h);
+    if ((vep::fmt_is_semiplanar(fmt) || vep::fmt_bytes_per_sample(fmt) == 2) && h < 8) return fail(VEP_ERR_GEOMETRY, "nv12/nv21/10-bit height %d < 8", h);
     if (ring_depth < 1) ring_depth = 1;
     if (ring_depth > 64) return fail(VEP_ERR_INVALID_ARG, "ring_depth %d > 64", ring_depth);
     DeviceGuard g(c->device);
@@ -575,12 +580,13 @@ extern "C" int vep_stream_open(vep_ctx *c, int stream_id, int fmt, int w, int h,
     Stream *s = new (std::nothrow) Stream();
     if (!s) return fail(VEP_ERR_NOMEM, "out of host memory");
     s->id = stream_id; s->fmt = fmt; s->w = w; s->h = h; s->ring = ring_depth;
-    const size_t ysz = (size_t)w * h;
+    const size_t bps = vep::fmt_bytes_per_sample(fmt);
+    const size_t ysz = (size_t)w * h * bps;       // bytes of the luma plane (chroma planes scale with it)
     s->off_c0 = align_up(ysz, 256);
     const size_t csz = vep::fmt_is_422(fmt) ? ysz / 2 : ysz / 4;   // bytes of one planar chroma plane
     if (vep::fmt_is_semiplanar(fmt)) { s->off_c1 = 0; s->in_bytes = s->off_c0 + ysz / 2; }
     else { s->off_c1 = s->off_c0 + align_up(csz, 256); s->in_bytes = s->off_c1 + csz; }
-    s->out_bytes = ysz * 3;
+    s->out_bytes = (size_t)w * h * 3;
     s->in_slot = align_up(s->in_bytes, 4096);
     s->out_slot = align_up(kHdrRoom + s->out_bytes + kTrailerRoom, 4096);
     const int ns = ring_depth + VEP_MAX_TICKS_IN_FLIGHT + 2;   // ring + ticks in flight + one filling + slack
@@ -644,8 +650,9 @@ static int claim_slot(Stream *s) {
 
 static void plane_ptrs(Stream *s, uint8_t *base, uint8_t *pl[3], int32_t st[3]) {
     const bool semi = vep::fmt_is_semiplanar(s->fmt);
+    const int bps = vep::fmt_bytes_per_sample(s->fmt);
     pl[0] = base; pl[1] = base + s->off_c0; pl[2] = semi ? nullptr : base + s->off_c1;
-    st[0] = s->w; st[1] = semi ? s->w : s->w / 2; st[2] = semi ? 0 : s->w / 2;
+    st[0] = s->w * bps; st[1] = semi ? s->w : s->w / 2 * bps; st[2] = semi ? 0 : s->w / 2 * bps;
 }
 
 extern "C" int vep_acquire_input(vep_ctx *c, int stream_id, uint8_t *plane_out[3], int32_t stride_out[3]) {
@@ -713,9 +720,10 @@ extern "C" int vep_submit(vep_ctx *c, int stream_id, const uint8_t *const plane[
     }
     const bool semi = vep::fmt_is_semiplanar(s->fmt);
     if (!plane || !stride || !plane[0] || !plane[1] || (!semi && !plane[2])) return fail(VEP_ERR_INVALID_ARG, "null plane");
-    const int cw = semi ? s->w : s->w / 2;
+    const int bps = vep::fmt_bytes_per_sample(s->fmt);
+    const int cw = (semi ? s->w : s->w / 2) * bps;      // chroma row bytes
     const int crows = vep::fmt_is_422(s->fmt) ? s->h : s->h / 2;
-    if (stride[0] < s->w || stride[1] < cw || (!semi && stride[2] < cw)) return fail(VEP_ERR_GEOMETRY, "stride smaller than row");
+    if (stride[0] < s->w * bps || stride[1] < cw || (!semi && stride[2] < cw)) return fail(VEP_ERR_GEOMETRY, "stride smaller than row");
     uint8_t *pl[3];
     int32_t st[3];
     {
@@ -725,7 +733,7 @@ extern "C" int vep_submit(vep_ctx *c, int stream_id, const uint8_t *const plane[
         plane_ptrs(s, s->slots[i].h_in, pl, st);
     }
     // the copy runs outside the lock: one producer per stream
-    copy_plane(pl[0], st[0], plane[0], stride[0], s->w, s->h);
+    copy_plane(pl[0], st[0], plane[0], stride[0], s->w * bps, s->h);
     copy_plane(pl[1], st[1], plane[1], stride[1], cw, crows);
     if (!semi) copy_plane(pl[2], st[2], plane[2], stride[2], cw, crows);
     return vep_commit_input(c, stream_id, meta);
@@ -784,8 +792,9 @@ static int tick_enqueue(vep_ctx *c, TickRec &t, int *n_frames) {
             c->stats.h2d_bytes += (int64_t)s->in_bytes;
             vep_frame_desc d{};
             const bool semi = vep::fmt_is_semiplanar(s->fmt);
+            const int bps = vep::fmt_bytes_per_sample(s->fmt);
             d.plane[0] = sl.d_in; d.plane[1] = sl.d_in + s->off_c0; d.plane[2] = semi ? nullptr : sl.d_in + s->off_c1;
-            d.stride[0] = s->w; d.stride[1] = semi ? s->w : s->w / 2; d.stride[2] = semi ? 0 : s->w / 2;
+            d.stride[0] = s->w * bps; d.stride[1] = semi ? s->w : s->w / 2 * bps; d.stride[2] = semi ? 0 : s->w / 2 * bps;
             d.dst = sl.d_out; d.dst_stride = 3 * s->w; d.width = s->w; d.height = s->h; d.fmt = s->fmt; d.convert = 1;
             descs.push_back(d);
             write_framing(s, sl);
@@ -939,16 +948,19 @@ static CtaWork g_noalloc_h_work[VEP_NOALLOC_MAX_CTAS];
 
 // Validation + table row for one descriptor; mirrors build_tables() without touching the heap.
 static int noalloc_frame(const vep_frame_desc &s, int i, FrameDev &f) {
-    if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_YUVJ422P) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
+    if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_YUV420P10LE) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
     const int w = s.width, h = s.height;
     if (w <= 0 || h <= 0 || w > kMaxDim || h > kMaxDim || (w & 1) || (h & 1))
         return fail(VEP_ERR_GEOMETRY, "desc %d: %dx%d — 4:2:0 needs even, positive dimensions <= %d", i, w, h, kMaxDim);
     const bool nv12 = vep::fmt_is_semiplanar(s.fmt);
-    if (nv12 && h < 8) return fail(VEP_ERR_GEOMETRY, "desc %d: nv12 height %d < 8", i, h);
+    const int bps = vep::fmt_bytes_per_sample(s.fmt);
+    if ((nv12 || bps == 2) && h < 8) return fail(VEP_ERR_GEOMETRY, "desc %d: nv12/nv21/10-bit height %d < 8", i, h);
     if (!s.plane[0] || !s.plane[1] || (!nv12 && !s.plane[2]) || !s.dst) return fail(VEP_ERR_INVALID_ARG, "desc %d: null plane or dst", i);
-    const int cw = nv12 ? w : w / 2;
-    if (s.stride[0] < w || s.stride[1] < cw || (!nv12 && s.stride[2] < cw) || s.dst_stride < 3 * w)
+    const int cw = (nv12 ? w : w / 2) * bps;
+    if (s.stride[0] < w * bps || s.stride[1] < cw || (!nv12 && s.stride[2] < cw) || s.dst_stride < 3 * w)
         return fail(VEP_ERR_GEOMETRY, "desc %d: a stride is smaller than its row", i);
+    if (bps == 2 && ((s.stride[0] | s.stride[1] | s.stride[2]) & 1 || !aligned(s.plane[0], 2) || !aligned(s.plane[1], 2) || !aligned(s.plane[2], 2)))
+        return fail(VEP_ERR_GEOMETRY, "desc %d: 16-bit samples need 2-byte aligned planes and even strides", i);
     f = FrameDev{};
     f.y = s.plane[0]; f.c0 = s.plane[1]; f.c1 = nv12 ? nullptr : s.plane[2]; f.dst = s.dst;
     f.sy = s.stride[0]; f.sc0 = s.stride[1]; f.sc1 = nv12 ? 0 : s.stride[2]; f.sd = s.dst_stride;
@@ -957,7 +969,7 @@ static int noalloc_frame(const vep_frame_desc &s, int i, FrameDev &f) {
     const bool vec = (w % 16 == 0) && aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
                      (nv12 || (aligned(f.c1, 8) && f.sc1 % 8 == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
     f.fast = vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;   // the table-driven kernel knows these two paths
-    if (vep::fmt_is_422(s.fmt)) f.fast = vep::PATH_GENERIC;   // ... and converts 4:2:2 on the scalar one
+    if (vep::fmt_is_422(s.fmt) || bps == 2) f.fast = vep::PATH_GENERIC;   // ... and converts 4:2:2 / 10-bit on the scalar one
     f.fast_tbl = f.fast;
     f.segs = (w + vep::kSegPx - 1) / vep::kSegPx;
     return VEP_OK;

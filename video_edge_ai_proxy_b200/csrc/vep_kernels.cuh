@@ -26,10 +26,11 @@ constexpr int kSegPx = 512;                       // pixels per warp item row (3
 constexpr int kSegBytes = kSegPx * 3;             // 1536 output bytes per row of an item
 constexpr int kGenericBlocksPerCta = 1024;        // 2x2 blocks per CTA on the generic path
 
-enum : int { FMT_YUV420P = 0, FMT_YUVJ420P = 1, FMT_NV12 = 2, FMT_NV21 = 3, FMT_YUV422P = 4, FMT_YUVJ422P = 5 };
+enum : int { FMT_YUV420P = 0, FMT_YUVJ420P = 1, FMT_NV12 = 2, FMT_NV21 = 3, FMT_YUV422P = 4, FMT_YUVJ422P = 5, FMT_YUV420P10 = 6 };
 __host__ __device__ constexpr bool fmt_is_semiplanar(int f) { return f == FMT_NV12 || f == FMT_NV21; }
 __host__ __device__ constexpr bool fmt_is_422(int f) { return f == FMT_YUV422P || f == FMT_YUVJ422P; }
 __host__ __device__ constexpr bool fmt_is_full_range(int f) { return f == FMT_YUVJ420P || f == FMT_YUVJ422P; }
+__host__ __device__ constexpr int fmt_bytes_per_sample(int f) { return f == FMT_YUV420P10 ? 2 : 1; }
 
 enum : int { PATH_GENERIC = 0, PATH_VECTOR = 1, PATH_BULK = 2 };
 
@@ -81,6 +82,7 @@ struct KB {
 
 __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) { return __byte_perm(a, b, sel); }
 __device__ __forceinline__ uint32_t byte_of(uint32_t w, int k) { return __byte_perm(w, 0, 0x4440 | k); }
+__device__ __forceinline__ uint32_t word_of(const uint4 &v, int i) { return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w; }
 
 __device__ __forceinline__ uint4 ld_stream_v4(const uint8_t *p) {
     uint4 r;
@@ -125,15 +127,9 @@ __device__ __forceinline__ ChromaPair chroma_a_sum2(uint32_t su, uint32_t sv) {
                        (int)su * (M::gu_mul / 2) + M::gu_add, (int)sv * (M::gv_mul / 2) + M::gv_add);
 }
 
-// 4 luma samples (one 32-bit word) + the two chroma pairs covering them -> 12 output bytes
-template <bool FULL>
-__device__ __forceinline__ void luma4_a(uint32_t yw, const ChromaPair &P, const ChromaPair &Q,
+// four luma IMAD results (upper halves = y - 1024) + the two chroma pairs covering them -> 12 output bytes
+__device__ __forceinline__ void pack4_a(int t0, int t1, int t2, int t3, const ChromaPair &P, const ChromaPair &Q,
                                         uint32_t &w0, uint32_t &w1, uint32_t &w2) {
-    using M = KM<FULL>;
-    const int t0 = (int)byte_of(yw, 0) * M::y_mul + M::y_add;
-    const int t1 = (int)byte_of(yw, 1) * M::y_mul + M::y_add;
-    const int t2 = (int)byte_of(yw, 2) * M::y_mul + M::y_add;
-    const int t3 = (int)(yw >> 24) * M::y_mul + M::y_add;
     const uint32_t yp = prmt((uint32_t)t0, (uint32_t)t1, 0x7632);   // [y0-1024, y1-1024] as s16x2
     const uint32_t yq = prmt((uint32_t)t2, (uint32_t)t3, 0x7632);
     const uint32_t bp = add_sat_u8_x2(yp, P.cb2), gp = add_sat_u8_x2(yp, P.cg2), rp = add_sat_u8_x2(yp, P.cr2);
@@ -146,7 +142,19 @@ __device__ __forceinline__ void luma4_a(uint32_t yw, const ChromaPair &P, const 
     w2 = prmt(bgq, rq, 0x6324);            // R2 B3 G3 R3
 }
 
-// formula B on one 32-bit word of luma; kb/kg/kr = base + d*cy for the two chroma columns
+// 4 luma samples (one 32-bit word) + the two chroma pairs covering them -> 12 output bytes
+template <bool FULL>
+__device__ __forceinline__ void luma4_a(uint32_t yw, const ChromaPair &P, const ChromaPair &Q,
+                                        uint32_t &w0, uint32_t &w1, uint32_t &w2) {
+    using M = KM<FULL>;
+    const int t0 = (int)byte_of(yw, 0) * M::y_mul + M::y_add;
+    const int t1 = (int)byte_of(yw, 1) * M::y_mul + M::y_add;
+    const int t2 = (int)byte_of(yw, 2) * M::y_mul + M::y_add;
+    const int t3 = (int)(yw >> 24) * M::y_mul + M::y_add;
+    pack4_a(t0, t1, t2, t3, P, Q, w0, w1, w2);
+}
+
+// formula B; kb/kg/kr = base + d*cy for one chroma column pair
 struct ChromaB { int kb, kg, kr; };
 __device__ __forceinline__ ChromaB chroma_b(int u, int v) {
     ChromaB c;
@@ -161,10 +169,9 @@ __device__ __forceinline__ ChromaB chroma_b(int u, int v) {
 __device__ __forceinline__ uint32_t clamp_pair_hi(int a, int b) {   // [sat_u8(a>>16), sat_u8(b>>16)] as s16x2
     return __vimin_s16x2_relu(prmt((uint32_t)a, (uint32_t)b, 0x7632), 0x00ff00ffu);
 }
-__device__ __forceinline__ void luma4_b(uint32_t yw, const ChromaB &P, const ChromaB &Q,
+// y0..y3 are luma * cy (formula B), P/Q the chroma offsets of the two column pairs
+__device__ __forceinline__ void pack4_b(int y0, int y1, int y2, int y3, const ChromaB &P, const ChromaB &Q,
                                         uint32_t &w0, uint32_t &w1, uint32_t &w2) {
-    const int y0 = (int)byte_of(yw, 0) * KB::cy, y1 = (int)byte_of(yw, 1) * KB::cy;
-    const int y2 = (int)byte_of(yw, 2) * KB::cy, y3 = (int)(yw >> 24) * KB::cy;
     const uint32_t bp = clamp_pair_hi(y0 + P.kb, y1 + P.kb), gp = clamp_pair_hi(y0 + P.kg, y1 + P.kg),
                    rp = clamp_pair_hi(y0 + P.kr, y1 + P.kr);
     const uint32_t bq = clamp_pair_hi(y2 + Q.kb, y3 + Q.kb), gq = clamp_pair_hi(y2 + Q.kg, y3 + Q.kg),
@@ -175,8 +182,55 @@ __device__ __forceinline__ void luma4_b(uint32_t yw, const ChromaB &P, const Chr
     w1 = prmt(x, bgq, 0x5410);
     w2 = prmt(bgq, rq, 0x6324);
 }
+__device__ __forceinline__ void luma4_b(uint32_t yw, const ChromaB &P, const ChromaB &Q, uint32_t &w0, uint32_t &w1, uint32_t &w2) {
+    pack4_b((int)byte_of(yw, 0) * KB::cy, (int)byte_of(yw, 1) * KB::cy, (int)byte_of(yw, 2) * KB::cy, (int)(yw >> 24) * KB::cy, P, Q, w0, w1, w2);
+}
 
-__device__ __forceinline__ uint32_t word_of(const uint4 &v, int i) { return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w; }
+// ---- yuv420p10le: 10-bit samples in 16-bit containers.  Same stages with 11-bit terms: luma (Y<<1), odd rows (u<<1),
+//      even rows (u_above + u); rows H-2/H-1 use formula B on y = (Y+2)>>2, u = min((blend+8192)>>14, 255). ----
+struct P10 {   // multipliers: the 8-bit constants carry "<<3", 10-bit samples need "<<1" (a quarter), sums need "<<0"
+    using M = KM<false>;
+    static constexpr int y_mul = M::y_mul / 4, b_mul = M::b_mul / 4, r_mul = M::r_mul / 4, gu_mul = M::gu_mul / 4, gv_mul = M::gv_mul / 4;
+};
+__device__ __forceinline__ ChromaPair chroma_p10(uint32_t u, uint32_t v, int shift /*0: (u<<1), 1: sum of two rows*/) {
+    using M = KM<false>;
+    const int bm = P10::b_mul >> shift, rm = P10::r_mul >> shift, gum = P10::gu_mul / (1 << shift), gvm = P10::gv_mul / (1 << shift);
+    return chroma_pack((int)u * bm + M::b_add, (int)v * rm + M::r_add, (int)u * gum + M::gu_add, (int)v * gvm + M::gv_add);
+}
+// one group of 4 px x 2 rows: ya/yb = two 32-bit words each (4 samples), cu/cv/pu/pv = one word each (2 samples)
+__device__ __forceinline__ void group_p10(uint32_t ya0, uint32_t ya1, uint32_t yb0, uint32_t yb1, uint32_t cu, uint32_t cv,
+                                          uint32_t pu, uint32_t pv, bool tail, uint32_t *o0, uint32_t *o1) {
+    using M = KM<false>;
+    const uint32_t u0 = cu & 0xffffu, u1 = cu >> 16, v0 = cv & 0xffffu, v1 = cv >> 16;
+    const uint32_t a0 = pu & 0xffffu, a1 = pu >> 16, b0 = pv & 0xffffu, b1 = pv >> 16;     // row above
+    const int ye0 = ya0 & 0xffffu, ye1 = ya0 >> 16, ye2 = ya1 & 0xffffu, ye3 = ya1 >> 16;
+    const int yo0 = yb0 & 0xffffu, yo1 = yb0 >> 16, yo2 = yb1 & 0xffffu, yo3 = yb1 >> 16;
+    if (!tail) {
+        const ChromaPair Pe = chroma_p10(a0 + u0, b0 + v0, 1), Qe = chroma_p10(a1 + u1, b1 + v1, 1);
+        const ChromaPair Po = chroma_p10(u0, v0, 0), Qo = chroma_p10(u1, v1, 0);
+        pack4_a(ye0 * P10::y_mul + M::y_add, ye1 * P10::y_mul + M::y_add, ye2 * P10::y_mul + M::y_add, ye3 * P10::y_mul + M::y_add, Pe, Qe, o0[0], o0[1], o0[2]);
+        pack4_a(yo0 * P10::y_mul + M::y_add, yo1 * P10::y_mul + M::y_add, yo2 * P10::y_mul + M::y_add, yo3 * P10::y_mul + M::y_add, Po, Qo, o1[0], o1[1], o1[2]);
+    } else {
+        const ChromaB Pe = chroma_b(min((int)(a0 * 1024u + u0 * 3072u + 8192u) >> 14, 255), min((int)(b0 * 1024u + v0 * 3072u + 8192u) >> 14, 255));
+        const ChromaB Qe = chroma_b(min((int)(a1 * 1024u + u1 * 3072u + 8192u) >> 14, 255), min((int)(b1 * 1024u + v1 * 3072u + 8192u) >> 14, 255));
+        const ChromaB Po = chroma_b(min((int)(u0 + 2) >> 2, 255), min((int)(v0 + 2) >> 2, 255)), Qo = chroma_b(min((int)(u1 + 2) >> 2, 255), min((int)(v1 + 2) >> 2, 255));
+        pack4_b(((ye0 + 2) >> 2) * KB::cy, ((ye1 + 2) >> 2) * KB::cy, ((ye2 + 2) >> 2) * KB::cy, ((ye3 + 2) >> 2) * KB::cy, Pe, Qe, o0[0], o0[1], o0[2]);
+        pack4_b(((yo0 + 2) >> 2) * KB::cy, ((yo1 + 2) >> 2) * KB::cy, ((yo2 + 2) >> 2) * KB::cy, ((yo3 + 2) >> 2) * KB::cy, Po, Qo, o1[0], o1[1], o1[2]);
+    }
+}
+// one lane's 16 px x 2 rows: ya/yb two uint4 each (16 samples), cu/cv/pu/pv one uint4 each (8 samples)
+__device__ __forceinline__ void compute_p10(const uint4 &ya_lo, const uint4 &ya_hi, const uint4 &yb_lo, const uint4 &yb_hi, const uint4 &cu,
+                                            const uint4 &cv, const uint4 &pu, const uint4 &pv, bool tail, uint32_t (&o0)[12], uint32_t (&o1)[12]) {
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        const uint4 &a = g < 2 ? ya_lo : ya_hi, &b = g < 2 ? yb_lo : yb_hi;
+        const int h = (g & 1) * 2;
+        group_p10(word_of(a, h), word_of(a, h + 1), word_of(b, h), word_of(b, h + 1), word_of(cu, g), word_of(cv, g), word_of(pu, g), word_of(pv, g),
+                  tail, &o0[3 * g], &o1[3 * g]);
+    }
+}
+
+
 
 // ---- one lane's 16 px x 2 rows, planar: uu/vv hold 8 chroma samples each ---------------------------
 template <bool FULL>
@@ -265,7 +319,33 @@ __device__ __forceinline__ void px_b(int Y, int u, int v, uint8_t *d) {
     d[0] = sat8((Y * KB::cy + c.kb) >> 16); d[1] = sat8((Y * KB::cy + c.kg) >> 16); d[2] = sat8((Y * KB::cy + c.kr) >> 16);
 }
 
+__device__ __forceinline__ void px_a10(int Y, int Uw, int Vw, uint8_t *d) {   // 11-bit terms: Y = sample<<1, Uw/Vw already "- 1024"
+    using K = KA<false>;
+    const int y = ((Y - K::yOff) * K::yC) >> 16;
+    const int cb = (Uw * K::ub) >> 16, cr = (Vw * K::vr) >> 16;
+    const int cg = ((Uw * K::ug) >> 16) + ((Vw * K::vg) >> 16);
+    d[0] = sat8(y + cb); d[1] = sat8(y + cg); d[2] = sat8(y + cr);
+}
+__device__ __forceinline__ void generic_block_p10(const FrameDev &f, int bx, int by) {
+    const uint16_t *y0 = reinterpret_cast<const uint16_t *>(f.y + (size_t)(2 * by) * f.sy) + 2 * bx;
+    const uint16_t *y1 = reinterpret_cast<const uint16_t *>(f.y + (size_t)(2 * by + 1) * f.sy) + 2 * bx;
+    uint8_t *d0 = f.dst + (size_t)(2 * by) * f.sd + 6 * bx, *d1 = d0 + f.sd;
+    const int up = by > 0 ? by - 1 : 0;
+    const int u = reinterpret_cast<const uint16_t *>(f.c0 + (size_t)by * f.sc0)[bx], v = reinterpret_cast<const uint16_t *>(f.c1 + (size_t)by * f.sc1)[bx];
+    const int pu = reinterpret_cast<const uint16_t *>(f.c0 + (size_t)up * f.sc0)[bx], pv = reinterpret_cast<const uint16_t *>(f.c1 + (size_t)up * f.sc1)[bx];
+    if (by != (f.h >> 1) - 1) {
+        px_a10(y0[0] << 1, pu + u - 1024, pv + v - 1024, d0); px_a10(y0[1] << 1, pu + u - 1024, pv + v - 1024, d0 + 3);
+        px_a10(y1[0] << 1, (u << 1) - 1024, (v << 1) - 1024, d1); px_a10(y1[1] << 1, (u << 1) - 1024, (v << 1) - 1024, d1 + 3);
+    } else {
+        const int ue = min((pu * 1024 + u * 3072 + 8192) >> 14, 255), ve = min((pv * 1024 + v * 3072 + 8192) >> 14, 255);
+        const int uo = min((u + 2) >> 2, 255), vo = min((v + 2) >> 2, 255);
+        px_b((y0[0] + 2) >> 2, ue, ve, d0); px_b((y0[1] + 2) >> 2, ue, ve, d0 + 3);
+        px_b((y1[0] + 2) >> 2, uo, vo, d1); px_b((y1[1] + 2) >> 2, uo, vo, d1 + 3);
+    }
+}
+
 __device__ __forceinline__ void generic_block(const FrameDev &f, int bx, int by) {
+    if (f.fmt == FMT_YUV420P10) { generic_block_p10(f, bx, by); return; }
     const uint8_t *y0 = f.y + (size_t)(2 * by) * f.sy + 2 * bx, *y1 = y0 + f.sy;
     uint8_t *d0 = f.dst + (size_t)(2 * by) * f.sd + 6 * bx, *d1 = d0 + f.sd;
     if (!fmt_is_semiplanar(f.fmt)) {
@@ -450,8 +530,9 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     uint4 ya[RPT], yb[RPT], ca[RPT];   // ca: planar {U.lo,U.hi,V.lo,V.hi}; nv12: the 16 interleaved chroma bytes
     uint4 pu = make_uint4(0, 0, 0, 0);
     const bool nv12 = fmt_is_semiplanar(fmt);
+    const bool p10 = fmt == FMT_YUV420P10;               // 16-bit containers: loaded per row pair below, not here
     const int cshift = fmt_is_422(fmt) ? 1 : 0;           // 4:2:2: chroma row of luma row j is row j, not j/2
-    if (active) {
+    if (active && !p10) {
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
             const int rp = min(rp0 + r, hp - 1);            // clamp: an odd tail group re-reads the last pair (not stored)
@@ -477,7 +558,22 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     for (int r = 0; r < RPT; ++r) {
         const int rp = rp0 + r;
         if (rp >= hp) break;                                // warp-uniform
-        if (active && cshift) {
+        if (active && p10) {
+            // 10-bit: 32 B of luma per row and lane, 16 B per chroma plane; the row above feeds the even row
+            const uint8_t *yr = f.y + (size_t)(2 * rp) * f.sy + 2 * x;
+            const uint4 a_lo = ld_stream_v4(yr), a_hi = ld_stream_v4(yr + 16), b_lo = ld_stream_v4(yr + f.sy), b_hi = ld_stream_v4(yr + f.sy + 16);
+            const int upr = rp > 0 ? rp - 1 : 0;
+            const uint4 cu = ld_stream_v4(f.c0 + (size_t)rp * f.sc0 + x), cv = ld_stream_v4(f.c1 + (size_t)rp * f.sc1 + x);
+            const uint4 pu10 = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)upr * f.sc0 + x));
+            const uint4 pv10 = __ldg(reinterpret_cast<const uint4 *>(f.c1 + (size_t)upr * f.sc1 + x));
+            uint32_t o0[12], o1[12];
+            compute_p10(a_lo, a_hi, b_lo, b_hi, cu, cv, pu10, pv10, rp == hp - 1, o0, o1);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                *reinterpret_cast<uint4 *>(t0 + lane * 48 + k * 16) = make_uint4(o0[4 * k], o0[4 * k + 1], o0[4 * k + 2], o0[4 * k + 3]);
+                *reinterpret_cast<uint4 *>(t1 + lane * 48 + k * 16) = make_uint4(o1[4 * k], o1[4 * k + 1], o1[4 * k + 2], o1[4 * k + 3]);
+            }
+        } else if (active && cshift) {
             // 4:2:2: the odd luma row has a chroma row of its own.  One row at a time (park it, then the next)
             // keeps this secondary format from raising the register count of the 4:2:0 path.
             uint32_t o[12];

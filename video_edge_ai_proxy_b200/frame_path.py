@@ -52,10 +52,10 @@ def _plane_ptrs(planes: Sequence[np.ndarray]):
     ptrs = (C.c_void_p * 3)()
     strides = (C.c_int32 * 3)()
     for i, p in enumerate(planes):
-        if p.dtype != np.uint8 or p.ndim != 2 or p.strides[1] != 1:
-            raise ValueError("planes must be 2-D uint8 arrays with unit column stride")
+        if p.dtype not in (np.uint8, np.uint16) or p.ndim != 2 or p.strides[1] != p.itemsize:
+            raise ValueError("planes must be 2-D uint8 (uint16 for 10-bit formats) arrays with contiguous rows")
         ptrs[i] = p.ctypes.data
-        strides[i] = p.strides[0]
+        strides[i] = p.strides[0]          # bytes, as in AVFrame.linesize
     return ptrs, strides
 
 
@@ -76,11 +76,13 @@ def desc_from_tensors(fmt: str, planes, out, convert=True) -> FrameDesc:
     planes: (Y,U,V) or (Y,UV) 2-D tensors; out: (H,W,3) tensor."""
     h, w = int(planes[0].shape[0]), int(planes[0].shape[1])
     for t in list(planes) + [out]:
-        if not t.is_cuda or t.dtype.__str__() != "torch.uint8" or t.stride(-1) != 1:
-            raise ValueError("tensors must be CUDA uint8 with unit innermost stride")
+        if not t.is_cuda or t.stride(-1) != 1:
+            raise ValueError("tensors must be CUDA tensors with unit innermost stride")
+    if str(out.dtype) != "torch.uint8" or any(t.element_size() != (2 if fmt == "yuv420p10le" else 1) for t in planes):
+        raise ValueError("planes must be uint8 (16-bit elements for yuv420p10le), out uint8")
     if tuple(out.shape) != (h, w, 3) or out.stride(1) != 3:
         raise ValueError("out must be (H, W, 3) with packed pixels")
-    return desc_from_device_ptrs(fmt, w, h, [p.data_ptr() for p in planes], [p.stride(0) for p in planes],
+    return desc_from_device_ptrs(fmt, w, h, [p.data_ptr() for p in planes], [p.stride(0) * p.element_size() for p in planes],
                                  out.data_ptr(), out.stride(0), convert)
 
 
@@ -204,7 +206,8 @@ class FramePath:
         out = []
         for i, shp in enumerate(shapes):
             buf = (C.c_uint8 * (shp[0] * strides[i])).from_address(ptrs[i])
-            out.append(np.frombuffer(buf, np.uint8).reshape(shp[0], strides[i])[:, :shp[1]])
+            rows = np.frombuffer(buf, np.uint8).reshape(shp[0], strides[i])
+            out.append(rows.view(np.uint16)[:, :shp[1]] if fmt == "yuv420p10le" else rows[:, :shp[1]])
         return out
 
     def acquire_raw(self, device_id: str):

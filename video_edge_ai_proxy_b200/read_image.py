@@ -25,7 +25,7 @@ from . import global_vars
 from .frame_path import FramePath, make_meta
 from .gate import DecodeGate
 
-_SUPPORTED = ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p")
+_SUPPORTED = ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le")
 
 
 def planes_of(frame):
@@ -39,7 +39,10 @@ def planes_of(frame):
         a = np.frombuffer(p, np.uint8)
         ls = int(p.line_size)
         rows = int(getattr(p, "height", a.size // ls))
-        out.append(a[:rows * ls].reshape(rows, ls)[:, :int(p.width)])
+        a = a[:rows * ls].reshape(rows, ls)
+        if _name(getattr(frame.format, "name", frame.format)) == "yuv420p10le":
+            a = a.view(np.uint16)                       # 16-bit little-endian samples
+        out.append(a[:, :int(p.width)])
     return out
 
 

@@ -8,7 +8,7 @@ from __future__ import annotations
 
 import numpy as np
 
-FORMATS = ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p")
+FORMATS = ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le")
 
 
 def make_planes(fmt: str, w: int, h: int, seed: int, dist: str = "uniform"):
@@ -24,6 +24,12 @@ def make_planes(fmt: str, w: int, h: int, seed: int, dist: str = "uniform"):
         lo_y, hi_y, lo_c, hi_c = 16, 236, 16, 241
     else:
         raise ValueError(dist)
+    if fmt == "yuv420p10le":      # 10-bit samples in little-endian 16-bit containers (HEVC Main10 decodes to this)
+        s4 = lambda v: min(v * 4, 1024)
+        Y = rng.integers(s4(lo_y), s4(hi_y), (h, w), dtype=np.uint16)
+        U = rng.integers(s4(lo_c), s4(hi_c), (h // 2, w // 2), dtype=np.uint16)
+        V = rng.integers(s4(lo_c), s4(hi_c), (h // 2, w // 2), dtype=np.uint16)
+        return (Y, U, V)
     ch = h if fmt in ("yuv422p", "yuvj422p") else h // 2      # 4:2:2 keeps every chroma row
     Y = rng.integers(lo_y, hi_y, (h, w), dtype=np.uint8)
     U = rng.integers(lo_c, hi_c, (ch, w // 2), dtype=np.uint8)
