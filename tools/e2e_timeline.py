@@ -1,7 +1,7 @@
 """Diagnostic: where does a tick's wall time go in the host pipeline (submit / begin / wait)?"""
 import sys, time, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np
+
 from concurrent.futures import ThreadPoolExecutor
 from video_edge_ai_proxy_b200 import FramePath, make_meta
 from video_edge_ai_proxy_b200.synth import make_planes

@@ -14,7 +14,7 @@ All arithmetic runs in libvepb200.so's sm_100a kernels; nothing here converts pi
 from __future__ import annotations
 
 import ctypes as C
-from typing import Dict, Iterable, Optional, Sequence
+from typing import Dict, Optional, Sequence
 
 import numpy as np
 
