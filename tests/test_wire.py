@@ -78,3 +78,45 @@ def test_bad_arguments():
         videoframe_framing(make_meta(), 0, 10)
     with pytest.raises(ValueError):
         make_meta(frame_type="TOOLONGNAME")
+
+
+_REF_SCRIPT = r'''
+import os, sys
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, "/root/reference/python")
+import numpy as np
+from proto import video_streaming_pb2 as pb            # the reference's own generated module
+from video_edge_ai_proxy_b200 import make_meta, videoframe_framing
+rng = np.random.default_rng(5)
+for w, h in ((640, 480), (2, 2), (1920, 1080)):
+    f = dict(timestamp=int(rng.integers(0, 1 << 50)), pts=int(rng.integers(-1 << 40, 1 << 40)), dts=int(rng.integers(-5, 5)),
+             packet=int(rng.integers(0, 300)), keyframe=int(rng.integers(0, 1 << 20)), time_base=1 / 90000,
+             is_keyframe=bool(rng.integers(2)), is_corrupt=bool(rng.integers(2)), frame_type=str(rng.choice(["I", "P", "B", ""])))
+    pre, suf = videoframe_framing(make_meta(**f), w, h)
+    data = rng.integers(0, 256, w * h * 3, dtype=np.uint8).tobytes()
+    msg = pre + data + suf
+    vf = pb.VideoFrame(); vf.ParseFromString(msg)                       # what grpc_api.go:212-216 does with proto.Unmarshal
+    assert (vf.width, vf.height, vf.data) == (w, h, data)
+    for k, v in f.items():
+        assert getattr(vf, k) == v, (k, getattr(vf, k), v)
+    assert [(d.size, d.name) for d in vf.shape.dim] == [(h, "0"), (w, "1"), (3, "2")] and vf.device_id == ""
+    assert vf.SerializeToString() == msg                                # and what it re-sends is the same bytes
+    img = np.frombuffer(vf.data, dtype=np.uint8).reshape([d.size for d in vf.shape.dim])   # examples/opencv_display.py:48-53
+    assert img.shape == (h, w, 3)
+print("REF_PB2_OK")
+'''
+
+
+def test_reference_generated_module_parses_our_messages(tmp_path):
+    """Only where the reference tree is mounted (the build container): its own video_streaming_pb2 must parse and
+    re-serialize the C packer's output unchanged."""
+    import os
+    import subprocess
+    import sys
+    if not os.path.exists("/root/reference/python/proto/video_streaming_pb2.py"):
+        pytest.skip("reference tree not mounted on this machine")
+    script = tmp_path / "ref_parse.py"
+    script.write_text(_REF_SCRIPT)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, PROTOCOL_BUFFERS_PYTHON_IMPLEMENTATION="python")
+    out = subprocess.run([sys.executable, str(script), root], capture_output=True, text=True, env=env, timeout=120)
+    assert out.returncode == 0 and "REF_PB2_OK" in out.stdout, out.stdout + out.stderr
