@@ -248,7 +248,28 @@ def yuv420p10_to_bgr24(Y, U, V) -> np.ndarray:
     return out
 
 
+def yuv444p_to_bgr24(Y, U, V, full_range: bool = False) -> np.ndarray:
+    """4:4:4 planar.  libswscale turns on full chroma interpolation for it and runs its plain-C `yuv2rgb_full`
+    stage: per pixel, in wrapping 32-bit arithmetic with the SAME 13-bit coefficients as formula A,
+        Yt = ((Y << 9) - (yOff << 6)) * yC + (1 << 21)
+        B = Yt + ((U - 128) << 9) * ub,  G = Yt + ((U-128) << 9) * ug + ((V-128) << 9) * vg,  R = Yt + ((V-128) << 9) * vr
+    each clipped to [0, 2^30) (negative after wrap -> 0) and shifted right by 22.  One rounding per channel instead
+    of formula A's three floors; the limited-range blue term can wrap past 2^31 for bright saturated pixels and then
+    comes out 0 — reproduced, since the bar is the library's bytes.  Probed exact on uniform and extreme inputs."""
+    k = coeffs_simd(full_range)
+    Yi, Ui, Vi = Y.astype(np.int64), U.astype(np.int64), V.astype(np.int64)
+    Yt = ((Yi << 9) - (k["yOff"] << 6)) * k["yC"] + (1 << 21)
+    Uc, Vc = (Ui - 128) << 9, (Vi - 128) << 9
+    wrap = lambda a: ((a + (1 << 31)) % (1 << 32)) - (1 << 31)
+    fin = lambda a: np.clip(wrap(a) >> 22, 0, 255).astype(np.uint8)
+    return np.stack([fin(Yt + Uc * k["ub"]), fin(Yt + Uc * k["ug"] + Vc * k["vg"]), fin(Yt + Vc * k["vr"])], -1)
+
+
 def to_bgr24(fmt: str, planes) -> np.ndarray:
+    if fmt == "yuv444p":
+        return yuv444p_to_bgr24(planes[0], planes[1], planes[2], False)
+    if fmt == "yuvj444p":
+        return yuv444p_to_bgr24(planes[0], planes[1], planes[2], True)
     if fmt == "yuv420p10le":
         return yuv420p10_to_bgr24(planes[0], planes[1], planes[2])
     if fmt == "yuv422p":

@@ -33,6 +33,7 @@ def _load():
         _lib.port_yuv422p_to_bgr24.argtypes = [p, i, p, i, p, i, i, i, i, p, i]
         _lib.port_nv12_to_bgr24.argtypes = [p, i, p, i, i, i, p, i, i]
         _lib.port_yuv420p10_to_bgr24.argtypes = [p, i, p, i, p, i, i, i, p, i]
+        _lib.port_yuv444p_to_bgr24.argtypes = [p, i, p, i, p, i, i, i, i, p, i]
     return _lib
 
 
@@ -46,6 +47,11 @@ def to_bgr24(fmt: str, planes) -> np.ndarray:
         r = lib.port_yuv420p_to_bgr24(Y.ctypes.data, Y.strides[0], U.ctypes.data, U.strides[0],
                                       V.ctypes.data, V.strides[0], w, h,
                                       1 if fmt == "yuvj420p" else 0, out.ctypes.data, w * 3)
+    elif fmt in ("yuv444p", "yuvj444p"):
+        Y, U, V = planes
+        r = lib.port_yuv444p_to_bgr24(Y.ctypes.data, Y.strides[0], U.ctypes.data, U.strides[0],
+                                      V.ctypes.data, V.strides[0], w, h,
+                                      1 if fmt == "yuvj444p" else 0, out.ctypes.data, w * 3)
     elif fmt == "yuv420p10le":
         Y, U, V = planes
         r = lib.port_yuv420p10_to_bgr24(Y.ctypes.data, Y.strides[0], U.ctypes.data, U.strides[0],

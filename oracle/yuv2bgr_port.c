@@ -193,3 +193,26 @@ int port_yuv420p10_to_bgr24(const uint8_t *Y, int sy, const uint8_t *U, int su, 
     }
     return 0;
 }
+
+/* 4:4:4 planar (oracle/formulas.py: yuv444p_to_bgr24): swscale's plain-C full-chroma stage, wrapping 32-bit sums. */
+int port_yuv444p_to_bgr24(const uint8_t *Y, int sy, const uint8_t *U, int su, const uint8_t *V, int sv,
+                          int w, int h, int full_range, uint8_t *dst, int sd)
+{
+    if (w <= 0 || h <= 0 || (w & 1) || (h & 1)) return -1;
+    const simd_k *k = full_range ? &K_FULL : &K_LIMITED;
+    for (int j = 0; j < h; j++) {
+        const uint8_t *y = Y + (size_t)j * sy, *u = U + (size_t)j * su, *v = V + (size_t)j * sv;
+        uint8_t *d = dst + (size_t)j * sd;
+        for (int x = 0; x < w; x++) {
+            uint32_t yt = (uint32_t)((((int)y[x] << 9) - (k->yOff << 6)) * k->yC + (1 << 21));
+            int u9 = ((int)u[x] - 128) << 9, v9 = ((int)v[x] - 128) << 9;
+            int32_t b = (int32_t)(yt + (uint32_t)(u9 * k->ub));
+            int32_t g = (int32_t)(yt + (uint32_t)(u9 * k->ug) + (uint32_t)(v9 * k->vg));
+            int32_t r = (int32_t)(yt + (uint32_t)(v9 * k->vr));
+            d[3 * x + 0] = sat_u8(b >= 0 ? b >> 22 : -1);
+            d[3 * x + 1] = sat_u8(g >= 0 ? g >> 22 : -1);
+            d[3 * x + 2] = sat_u8(r >= 0 ? r >> 22 : -1);
+        }
+    }
+    return 0;
+}

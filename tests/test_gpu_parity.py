@@ -62,7 +62,7 @@ def test_exhaustive_yuv_triples_planar_both_ranges(path):
             assert np.array_equal(got[r0:r0 + 512], want), (fmt, r0)
 
 
-ALL_FORMATS = ["yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le"]
+ALL_FORMATS = ["yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le", "yuv444p", "yuvj444p"]
 TALL_ONLY = ("nv12", "nv21", "yuv420p10le")     # formats whose rule needs H >= 8
 
 
@@ -98,7 +98,7 @@ def test_live_libswscale_agrees_on_the_box(path):
     assert L.on_simd_path()
     for fmt, w, h in (("yuv420p", 1920, 1080), ("yuvj420p", 640, 480), ("nv12", 1280, 720), ("yuv420p", 50, 6),
                       ("nv21", 1920, 1080), ("yuv422p", 1280, 720), ("yuvj422p", 1920, 1080), ("yuvj422p", 50, 6),
-                      ("yuv420p10le", 1920, 1080), ("yuv420p10le", 50, 10)):
+                      ("yuv420p10le", 1920, 1080), ("yuv420p10le", 50, 10), ("yuv444p", 1920, 1080), ("yuvj444p", 50, 6)):
         planes = make_planes(fmt, w, h, 77)
         assert np.array_equal(gpu_convert(path, fmt, planes), L.to_bgr24(fmt, planes, w, h)), (fmt, w, h)
 
@@ -250,7 +250,7 @@ def test_tick_kernel_variants_bit_identical(env, small_frames):
             descs, keep = [], []
             for i in range(n):
                 fmt, w, h = (("yuv420p", 320, 240), ("nv12", 352, 288), ("yuvj420p", 160, 120), ("yuv420p", 50, 6),
-                             ("yuvj422p", 320, 240), ("nv21", 64, 48), ("yuv420p10le", 160, 120))[i % 7]
+                             ("yuvj422p", 320, 240), ("nv21", 64, 48), ("yuv420p10le", 160, 120), ("yuvj444p", 96, 64))[i % 8]
                 planes = make_planes(fmt, w, h, i)
                 t = [torch.from_numpy(q).cuda() for q in planes]
                 out = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")

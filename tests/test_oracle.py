@@ -41,7 +41,7 @@ def test_small_fixtures_numpy_and_c_port(small_frames):
         assert np.array_equal(P.to_bgr24(fmt, planes), out), (fmt, w, h)
 
 
-@pytest.mark.parametrize("row", range(34))
+@pytest.mark.parametrize("row", range(38))
 def test_numpy_restatement_matches_golden_table(golden_pixels, row):
     rows = golden_pixels["rows"]
     if row >= len(rows):
@@ -70,9 +70,22 @@ def test_ten_bit_extreme_samples_against_live_library():
         F.to_bgr24("yuv420p10le", make_planes("yuv420p10le", 16, 6, 0))
 
 
+def test_444_blue_wraparound_is_reproduced():
+    """Bright + saturated limited-range 4:4:4 pixels overflow swscale's 32-bit blue sum and come out 0, not 255."""
+    Y = np.full((2, 2), 255, np.uint8)
+    U = np.full((2, 2), 255, np.uint8)
+    V = np.full((2, 2), 128, np.uint8)
+    out = F.yuv444p_to_bgr24(Y, U, V, False)
+    assert out[0, 0, 0] == 0 and out[0, 0, 2] == 255
+    if L.available():
+        assert np.array_equal(L.to_bgr24("yuv444p", (Y, U, V), 2, 2), out)
+    assert np.array_equal(P.to_bgr24("yuv444p", (Y, U, V)), out)
+
+
 def test_c_port_matches_numpy_at_config_sizes():
     for fmt, w, h in (("yuv420p", 1920, 1080), ("yuvj420p", 1280, 720), ("nv12", 1920, 1080), ("nv12", 642, 10),
-                      ("nv21", 1280, 720), ("yuv422p", 642, 10), ("yuvj422p", 1920, 1080)):
+                      ("nv21", 1280, 720), ("yuv422p", 642, 10), ("yuvj422p", 1920, 1080), ("yuv420p10le", 1280, 720),
+                      ("yuv444p", 1280, 720), ("yuvj444p", 642, 10)):
         planes = make_planes(fmt, w, h, 3)
         assert np.array_equal(P.to_bgr24(fmt, planes), F.to_bgr24(fmt, planes)), (fmt, w, h)
 
@@ -120,7 +133,7 @@ def test_live_library_reproduces_survey_checksums(golden_pixels, fmt, w, h, seed
 
 @needs_live
 def test_live_vs_restatement_ragged_widths_and_heights():
-    for fmt in ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le"):
+    for fmt in ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le", "yuv444p", "yuvj444p"):
         for w in (2, 6, 14, 16, 18, 30, 34, 62, 130, 642):
             for h in (2, 4, 8, 10, 18):
                 if fmt in ("nv12", "nv21", "yuv420p10le") and h < 8:

@@ -93,7 +93,7 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1) 
     for (int i = 0; i < n; ++i) {
         const vep_frame_desc &s = d[i];
         if (!s.convert) continue;
-        if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_YUV420P10LE) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
+        if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_YUVJ444P) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
         const int w = s.width, h = s.height;
         if (w <= 0 || h <= 0 || w > kMaxDim || h > kMaxDim || (w & 1) || (h & 1))
             return fail(VEP_ERR_GEOMETRY, "desc %d: %dx%d — 4:2:0 needs even, positive dimensions <= %d", i, w, h, kMaxDim);
@@ -101,7 +101,7 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1) 
         const int bps = vep::fmt_bytes_per_sample(s.fmt);
         if ((nv12 || bps == 2) && h < 8) return fail(VEP_ERR_GEOMETRY, "desc %d: nv12/nv21/10-bit height %d < 8 (swscale changes its vertical chroma filter there)", i, h);
         if (!s.plane[0] || !s.plane[1] || (!nv12 && !s.plane[2]) || !s.dst) return fail(VEP_ERR_INVALID_ARG, "desc %d: null plane or dst", i);
-        const int cw = (nv12 ? w : w / 2) * bps;
+        const int cw = ((nv12 || vep::fmt_is_444(s.fmt)) ? w : w / 2) * bps;
         if (s.stride[0] < w * bps || s.stride[1] < cw || (!nv12 && s.stride[2] < cw) || s.dst_stride < 3 * w)
             return fail(VEP_ERR_GEOMETRY, "desc %d: a stride is smaller than its row", i);
         if (bps == 2 && ((s.stride[0] | s.stride[1] | s.stride[2]) & 1 || !aligned(s.plane[0], 2) || !aligned(s.plane[1], 2) || !aligned(s.plane[2], 2)))
@@ -115,6 +115,7 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1) 
                          (nv12 || (aligned(f.c1, ca) && f.sc1 % ca == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
         const bool bulk = vec && bps == 1 && (w % 32 == 0) && aligned(f.c0, 16) && f.sc0 % 16 == 0 && (nv12 || (aligned(f.c1, 16) && f.sc1 % 16 == 0));
         f.fast = bulk ? vep::PATH_BULK : vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;
+        if (vep::fmt_is_444(s.fmt)) f.fast = vep::PATH_GENERIC;   // 4:4:4 (rare from cameras) runs on the scalar path everywhere
         // only the tick kernel has a vector path for 4:2:2 and for 10-bit samples
         f.fast_tbl = (vep::fmt_is_422(s.fmt) || bps == 2) ? vep::PATH_GENERIC : f.fast;
         f.segs = (w + vep::kSegPx - 1) / vep::kSegPx;
@@ -136,7 +137,8 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1) 
         }
         if ((int64_t)t.total_items + items > (int64_t)1 << 30) return fail(VEP_ERR_INVALID_ARG, "batch too large");
         t.total_items += items;
-        t.alg_bytes += vep::fmt_is_422(s.fmt) ? (int64_t)w * h * 5 : bps == 2 ? (int64_t)w * h * 6 : (int64_t)w * h * 9 / 2;   // 4:2:2 reads 2 B/px, 10-bit 3 B/px
+        t.alg_bytes += vep::fmt_is_422(s.fmt) ? (int64_t)w * h * 5 : (bps == 2 || vep::fmt_is_444(s.fmt)) ? (int64_t)w * h * 6
+                                              : (int64_t)w * h * 9 / 2;   // read: 4:2:0 1.5, 4:2:2 2, 10-bit / 4:4:4 3 B/px
         t.n_converted++;
     }
     FrameDev sentinel{};
@@ -567,7 +569,7 @@ static Stream *find_stream(vep_ctx *c, int id) {
 
 extern "C" int vep_stream_open(vep_ctx *c, int stream_id, int fmt, int w, int h, int ring_depth) {
     if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
-    if (fmt < VEP_FMT_YUV420P || fmt > VEP_FMT_YUV420P10LE) return fail(VEP_ERR_INVALID_ARG, "unknown fmt %d", fmt);
+    if (fmt < VEP_FMT_YUV420P || fmt > VEP_FMT_YUVJ444P) return fail(VEP_ERR_INVALID_ARG, "unknown fmt %d", fmt);
     if (w <= 0 || h <= 0 || w > kMaxDim || h > kMaxDim || (w & 1) || (h & 1)) return fail(VEP_ERR_GEOMETRY, "%dx%d: need even, positive dimensions", w, h);
     if ((vep::fmt_is_semiplanar(fmt) || vep::fmt_bytes_per_sample(fmt) == 2) && h < 8) return fail(VEP_ERR_GEOMETRY, "nv12/nv21/10-bit height %d < 8", h);
     if (ring_depth < 1) ring_depth = 1;
@@ -583,7 +585,7 @@ extern "C" int vep_stream_open(vep_ctx *c, int stream_id, int fmt, int w, int h,
     const size_t bps = vep::fmt_bytes_per_sample(fmt);
     const size_t ysz = (size_t)w * h * bps;       // bytes of the luma plane (chroma planes scale with it)
     s->off_c0 = align_up(ysz, 256);
-    const size_t csz = vep::fmt_is_422(fmt) ? ysz / 2 : ysz / 4;   // bytes of one planar chroma plane
+    const size_t csz = vep::fmt_is_444(fmt) ? ysz : vep::fmt_is_422(fmt) ? ysz / 2 : ysz / 4;   // bytes of one planar chroma plane
     if (vep::fmt_is_semiplanar(fmt)) { s->off_c1 = 0; s->in_bytes = s->off_c0 + ysz / 2; }
     else { s->off_c1 = s->off_c0 + align_up(csz, 256); s->in_bytes = s->off_c1 + csz; }
     s->out_bytes = (size_t)w * h * 3;
@@ -651,8 +653,9 @@ static int claim_slot(Stream *s) {
 static void plane_ptrs(Stream *s, uint8_t *base, uint8_t *pl[3], int32_t st[3]) {
     const bool semi = vep::fmt_is_semiplanar(s->fmt);
     const int bps = vep::fmt_bytes_per_sample(s->fmt);
+    const int cwp = vep::fmt_is_444(s->fmt) ? s->w : s->w / 2;     // planar chroma samples per row
     pl[0] = base; pl[1] = base + s->off_c0; pl[2] = semi ? nullptr : base + s->off_c1;
-    st[0] = s->w * bps; st[1] = semi ? s->w : s->w / 2 * bps; st[2] = semi ? 0 : s->w / 2 * bps;
+    st[0] = s->w * bps; st[1] = semi ? s->w : cwp * bps; st[2] = semi ? 0 : cwp * bps;
 }
 
 extern "C" int vep_acquire_input(vep_ctx *c, int stream_id, uint8_t *plane_out[3], int32_t stride_out[3]) {
@@ -721,8 +724,8 @@ extern "C" int vep_submit(vep_ctx *c, int stream_id, const uint8_t *const plane[
     const bool semi = vep::fmt_is_semiplanar(s->fmt);
     if (!plane || !stride || !plane[0] || !plane[1] || (!semi && !plane[2])) return fail(VEP_ERR_INVALID_ARG, "null plane");
     const int bps = vep::fmt_bytes_per_sample(s->fmt);
-    const int cw = (semi ? s->w : s->w / 2) * bps;      // chroma row bytes
-    const int crows = vep::fmt_is_422(s->fmt) ? s->h : s->h / 2;
+    const int cw = ((semi || vep::fmt_is_444(s->fmt)) ? s->w : s->w / 2) * bps;      // chroma row bytes
+    const int crows = (vep::fmt_is_422(s->fmt) || vep::fmt_is_444(s->fmt)) ? s->h : s->h / 2;
     if (stride[0] < s->w * bps || stride[1] < cw || (!semi && stride[2] < cw)) return fail(VEP_ERR_GEOMETRY, "stride smaller than row");
     uint8_t *pl[3];
     int32_t st[3];
@@ -794,7 +797,8 @@ static int tick_enqueue(vep_ctx *c, TickRec &t, int *n_frames) {
             const bool semi = vep::fmt_is_semiplanar(s->fmt);
             const int bps = vep::fmt_bytes_per_sample(s->fmt);
             d.plane[0] = sl.d_in; d.plane[1] = sl.d_in + s->off_c0; d.plane[2] = semi ? nullptr : sl.d_in + s->off_c1;
-            d.stride[0] = s->w * bps; d.stride[1] = semi ? s->w : s->w / 2 * bps; d.stride[2] = semi ? 0 : s->w / 2 * bps;
+            const int cwp = vep::fmt_is_444(s->fmt) ? s->w : s->w / 2;
+            d.stride[0] = s->w * bps; d.stride[1] = semi ? s->w : cwp * bps; d.stride[2] = semi ? 0 : cwp * bps;
             d.dst = sl.d_out; d.dst_stride = 3 * s->w; d.width = s->w; d.height = s->h; d.fmt = s->fmt; d.convert = 1;
             descs.push_back(d);
             write_framing(s, sl);
@@ -948,7 +952,7 @@ static CtaWork g_noalloc_h_work[VEP_NOALLOC_MAX_CTAS];
 
 // Validation + table row for one descriptor; mirrors build_tables() without touching the heap.
 static int noalloc_frame(const vep_frame_desc &s, int i, FrameDev &f) {
-    if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_YUV420P10LE) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
+    if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_YUVJ444P) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
     const int w = s.width, h = s.height;
     if (w <= 0 || h <= 0 || w > kMaxDim || h > kMaxDim || (w & 1) || (h & 1))
         return fail(VEP_ERR_GEOMETRY, "desc %d: %dx%d — 4:2:0 needs even, positive dimensions <= %d", i, w, h, kMaxDim);
@@ -956,7 +960,7 @@ static int noalloc_frame(const vep_frame_desc &s, int i, FrameDev &f) {
     const int bps = vep::fmt_bytes_per_sample(s.fmt);
     if ((nv12 || bps == 2) && h < 8) return fail(VEP_ERR_GEOMETRY, "desc %d: nv12/nv21/10-bit height %d < 8", i, h);
     if (!s.plane[0] || !s.plane[1] || (!nv12 && !s.plane[2]) || !s.dst) return fail(VEP_ERR_INVALID_ARG, "desc %d: null plane or dst", i);
-    const int cw = (nv12 ? w : w / 2) * bps;
+    const int cw = ((nv12 || vep::fmt_is_444(s.fmt)) ? w : w / 2) * bps;
     if (s.stride[0] < w * bps || s.stride[1] < cw || (!nv12 && s.stride[2] < cw) || s.dst_stride < 3 * w)
         return fail(VEP_ERR_GEOMETRY, "desc %d: a stride is smaller than its row", i);
     if (bps == 2 && ((s.stride[0] | s.stride[1] | s.stride[2]) & 1 || !aligned(s.plane[0], 2) || !aligned(s.plane[1], 2) || !aligned(s.plane[2], 2)))
@@ -969,7 +973,7 @@ static int noalloc_frame(const vep_frame_desc &s, int i, FrameDev &f) {
     const bool vec = (w % 16 == 0) && aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
                      (nv12 || (aligned(f.c1, 8) && f.sc1 % 8 == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
     f.fast = vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;   // the table-driven kernel knows these two paths
-    if (vep::fmt_is_422(s.fmt) || bps == 2) f.fast = vep::PATH_GENERIC;   // ... and converts 4:2:2 / 10-bit on the scalar one
+    if (vep::fmt_is_422(s.fmt) || vep::fmt_is_444(s.fmt) || bps == 2) f.fast = vep::PATH_GENERIC;   // ... 4:2:2 / 4:4:4 / 10-bit on the scalar one
     f.fast_tbl = f.fast;
     f.segs = (w + vep::kSegPx - 1) / vep::kSegPx;
     return VEP_OK;

@@ -26,10 +26,11 @@ constexpr int kSegPx = 512;                       // pixels per warp item row (3
 constexpr int kSegBytes = kSegPx * 3;             // 1536 output bytes per row of an item
 constexpr int kGenericBlocksPerCta = 1024;        // 2x2 blocks per CTA on the generic path
 
-enum : int { FMT_YUV420P = 0, FMT_YUVJ420P = 1, FMT_NV12 = 2, FMT_NV21 = 3, FMT_YUV422P = 4, FMT_YUVJ422P = 5, FMT_YUV420P10 = 6 };
+enum : int { FMT_YUV420P = 0, FMT_YUVJ420P = 1, FMT_NV12 = 2, FMT_NV21 = 3, FMT_YUV422P = 4, FMT_YUVJ422P = 5, FMT_YUV420P10 = 6, FMT_YUV444P = 7, FMT_YUVJ444P = 8 };
 __host__ __device__ constexpr bool fmt_is_semiplanar(int f) { return f == FMT_NV12 || f == FMT_NV21; }
 __host__ __device__ constexpr bool fmt_is_422(int f) { return f == FMT_YUV422P || f == FMT_YUVJ422P; }
-__host__ __device__ constexpr bool fmt_is_full_range(int f) { return f == FMT_YUVJ420P || f == FMT_YUVJ422P; }
+__host__ __device__ constexpr bool fmt_is_444(int f) { return f == FMT_YUV444P || f == FMT_YUVJ444P; }
+__host__ __device__ constexpr bool fmt_is_full_range(int f) { return f == FMT_YUVJ420P || f == FMT_YUVJ422P || f == FMT_YUVJ444P; }
 __host__ __device__ constexpr int fmt_bytes_per_sample(int f) { return f == FMT_YUV420P10 ? 2 : 1; }
 
 enum : int { PATH_GENERIC = 0, PATH_VECTOR = 1, PATH_BULK = 2 };
@@ -344,8 +345,31 @@ __device__ __forceinline__ void generic_block_p10(const FrameDev &f, int bx, int
     }
 }
 
+// 4:4:4: swscale's plain-C "full chroma" stage — one rounding per channel, wrapping 32-bit arithmetic
+// (the limited-range blue term can pass 2^31 and then clips to 0, as in the library), every pixel its own chroma
+template <bool FULL>
+__device__ __forceinline__ void px_444(uint32_t Y, uint32_t U, uint32_t V, uint8_t *d) {
+    using K = KA<FULL>;
+    constexpr uint32_t yC9 = (uint32_t)K::yC << 9, kY = (uint32_t)(-(K::yOff << 6) * K::yC + (1 << 21));
+    const uint32_t yt = Y * yC9 + kY;
+    const int u9 = ((int)U - 128) << 9, v9 = ((int)V - 128) << 9;
+    const int b = (int)(yt + (uint32_t)(u9 * K::ub)), g = (int)(yt + (uint32_t)(u9 * K::ug) + (uint32_t)(v9 * K::vg)), r = (int)(yt + (uint32_t)(v9 * K::vr));
+    d[0] = sat8(b >> 22); d[1] = sat8(g >> 22); d[2] = sat8(r >> 22);
+}
+__device__ __forceinline__ void generic_block_444(const FrameDev &f, int bx, int by) {
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        const uint8_t *y = f.y + (size_t)(2 * by + r) * f.sy + 2 * bx, *u = f.c0 + (size_t)(2 * by + r) * f.sc0 + 2 * bx,
+                      *v = f.c1 + (size_t)(2 * by + r) * f.sc1 + 2 * bx;
+        uint8_t *d = f.dst + (size_t)(2 * by + r) * f.sd + 6 * bx;
+        if (f.fmt == FMT_YUVJ444P) { px_444<true>(y[0], u[0], v[0], d); px_444<true>(y[1], u[1], v[1], d + 3); }
+        else { px_444<false>(y[0], u[0], v[0], d); px_444<false>(y[1], u[1], v[1], d + 3); }
+    }
+}
+
 __device__ __forceinline__ void generic_block(const FrameDev &f, int bx, int by) {
     if (f.fmt == FMT_YUV420P10) { generic_block_p10(f, bx, by); return; }
+    if (fmt_is_444(f.fmt)) { generic_block_444(f, bx, by); return; }
     const uint8_t *y0 = f.y + (size_t)(2 * by) * f.sy + 2 * bx, *y1 = y0 + f.sy;
     uint8_t *d0 = f.dst + (size_t)(2 * by) * f.sd + 6 * bx, *d1 = d0 + f.sd;
     if (!fmt_is_semiplanar(f.fmt)) {

@@ -8,7 +8,7 @@ from __future__ import annotations
 
 import numpy as np
 
-FORMATS = ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le")
+FORMATS = ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le", "yuv444p", "yuvj444p")
 
 
 def make_planes(fmt: str, w: int, h: int, seed: int, dist: str = "uniform"):
@@ -30,10 +30,11 @@ def make_planes(fmt: str, w: int, h: int, seed: int, dist: str = "uniform"):
         U = rng.integers(s4(lo_c), s4(hi_c), (h // 2, w // 2), dtype=np.uint16)
         V = rng.integers(s4(lo_c), s4(hi_c), (h // 2, w // 2), dtype=np.uint16)
         return (Y, U, V)
-    ch = h if fmt in ("yuv422p", "yuvj422p") else h // 2      # 4:2:2 keeps every chroma row
+    ch = h if fmt in ("yuv422p", "yuvj422p", "yuv444p", "yuvj444p") else h // 2      # 4:2:2 / 4:4:4 keep every chroma row
+    cw = w if fmt in ("yuv444p", "yuvj444p") else w // 2                            # 4:4:4 keeps every chroma column
     Y = rng.integers(lo_y, hi_y, (h, w), dtype=np.uint8)
-    U = rng.integers(lo_c, hi_c, (ch, w // 2), dtype=np.uint8)
-    V = rng.integers(lo_c, hi_c, (ch, w // 2), dtype=np.uint8)
+    U = rng.integers(lo_c, hi_c, (ch, cw), dtype=np.uint8)
+    V = rng.integers(lo_c, hi_c, (ch, cw), dtype=np.uint8)
     if fmt in ("nv12", "nv21"):
         UV = np.empty((h // 2, w), np.uint8)
         UV[:, 0::2] = U if fmt == "nv12" else V
