@@ -36,6 +36,7 @@ if ROOT not in sys.path:
 METRIC = "1080p_bgr24_frames_per_sec"
 UNIT = "frames/s"
 ALG_BYTES_PER_PX = 4.5          # 1.5 B/px read (Y + U/4 + V/4) + 3 B/px written
+ALG_BYTES_BY_FMT = {"yuv422p": 5.0, "yuvj422p": 5.0, "yuv420p10le": 6.0, "yuv444p": 6.0, "yuvj444p": 6.0}   # formats that read more
 FALLBACK_HBM_GBS = 6650.0       # B200_PROFILING.md fallback when MEASURED_PEAKS.json is absent
 
 WORKLOADS = {
@@ -45,6 +46,9 @@ WORKLOADS = {
     "8x4k-nv12": (8, "nv12", 3840, 2160, "8 synthetic 3840x2160 NV12 cameras per GPU, every frame converted"),
     "8x4k-nv12-keyframe": (8, "nv12", 3840, 2160, "8 synthetic 3840x2160 NV12 cameras per GPU, key-frame-only: GOP 30, staggered phases, only key frames are converted (BASELINE configs[3])"),
     "mixed128-skip": (128, "yuv420p", 0, 0, "128-camera fleet per GPU: 43 x 640x480, 43 x 1280x720, 42 x 1920x1080 yuv420p, interval-skip: each camera converts a frame with p = 0.25 per tick (seeded Bernoulli, seed = tick) (BASELINE configs[4])"),
+    "16x1080p-yuvj422p": (16, "yuvj422p", 1920, 1080, "16 synthetic 1080p yuvj422p (MJPEG) cameras per GPU; 5 B/px"),
+    "16x1080p-yuv420p10le": (16, "yuv420p10le", 1920, 1080, "16 synthetic 1080p 10-bit 4:2:0 cameras per GPU; 6 B/px"),
+    "16x1080p-yuv444p": (16, "yuv444p", 1920, 1080, "16 synthetic 1080p 4:4:4 cameras per GPU (scalar kernel path); 6 B/px"),
     "64x1080p": (64, "yuv420p", 1920, 1080, "64 synthetic 1080p yuv420p cameras on one GPU (launch-overhead study, not a BASELINE config)"),
     "1x480p": (1, "yuv420p", 640, 480, "one 640x480 yuv420p stream (BASELINE configs[0])"),
 }
@@ -323,7 +327,7 @@ def run_gpu(args):
     n, fmt, w, h, desc = WORKLOADS[args.workload]
     cams = cameras_for_rank(args.workload, rank, world)
     sched = schedule_for(args.workload, len(cams))
-    alg = [int(ALG_BYTES_PER_PX * c["w"] * c["h"]) for c in cams]
+    alg = [int(ALG_BYTES_BY_FMT.get(c["fmt"], ALG_BYTES_PER_PX) * c["w"] * c["h"]) for c in cams]
     per_set_bytes = sum(alg)
     l2_bytes = torch.cuda.get_device_properties(dev).L2_cache_size
     n_sets = max(args.sets, 2, -(-3 * l2_bytes // per_set_bytes))   # footprint of the rotation >= 3x L2
@@ -531,7 +535,7 @@ def run_gpu(args):
         try:
             # bounded sample: ~20 s of CPU work in total, spread over the host threads
             frac = converted / max(args.steps * len(cams), 1)                                         # share of frames the gate lets through
-            est_ms = 1.6 * (per_set_bytes / 4.5) / (1920 * 1080) * (5.0 if fmt == "nv12" else 1.0) * max(frac, 0.01)
+            est_ms = 1.6 * (per_set_bytes / 4.5) / (1920 * 1080) * (1.0 if fmt in ("yuv420p", "yuvj420p") else 5.0) * max(frac, 0.01)
             cpu_steps = max(3, int(20000 / est_ms))
             fps, dt = cpu_frames_per_sec(cams, cpu_steps, 2, T, with_tobytes=True, sched=sched if n_pat > 1 else None)
             fps_scale, _ = cpu_frames_per_sec(cams, max(3, cpu_steps // 4), 1, T, with_tobytes=False, sched=sched if n_pat > 1 else None)
