@@ -45,7 +45,7 @@ typedef enum {
     VEP_FMT_YUVJ422P = 5,  /* planar 4:2:2, full range (what MJPEG cameras decode to) */
     VEP_FMT_YUV420P10LE = 6, /* planar 4:2:0, 10-bit samples (<= 1023) in little-endian 16-bit containers, limited range
                                (HEVC Main10); strides in BYTES; height >= 8 */
-    VEP_FMT_YUV444P = 7,   /* planar 4:4:4, limited range: chroma planes are W x H (scalar kernel path) */
+    VEP_FMT_YUV444P = 7,   /* planar 4:4:4, limited range: chroma planes are W x H */
     VEP_FMT_YUVJ444P = 8   /* planar 4:4:4, full range */
 } vep_pixfmt;
 

@@ -81,7 +81,7 @@ struct Tables {
 
 static inline bool aligned(const void *p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
 
-static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1) {
+static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1, bool vec444_ok = false) {
     if (n < 0 || (n > 0 && !d)) return fail(VEP_ERR_INVALID_ARG, "descs is null or n < 0");
     t.frames.clear();
     t.work.clear();
@@ -90,6 +90,10 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1) 
     t.total_items = 0;
     t.tick_cta_begin.clear();
     int tick_ctas = 0;
+    // the 4:4:4 vector path exists only in the format-specialised tick kernels: usable when the launch is single-format
+    int only_fmt = -2;
+    for (int i = 0; i < n; ++i) if (d[i].convert) only_fmt = (only_fmt == -2 || only_fmt == d[i].fmt) ? d[i].fmt : -1;
+    const bool homogeneous = only_fmt >= 0;
     for (int i = 0; i < n; ++i) {
         const vep_frame_desc &s = d[i];
         if (!s.convert) continue;
@@ -110,14 +114,14 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1) 
         f.y = s.plane[0]; f.c0 = s.plane[1]; f.c1 = nv12 ? nullptr : s.plane[2]; f.dst = s.dst;
         f.sy = s.stride[0]; f.sc0 = s.stride[1]; f.sc1 = nv12 ? 0 : s.stride[2]; f.sd = s.dst_stride;
         f.w = w; f.h = h; f.fmt = s.fmt;
-        const size_t ca = (nv12 || bps == 2) ? 16 : 8;
+        const size_t ca = (nv12 || bps == 2 || vep::fmt_is_444(s.fmt)) ? 16 : 8;
         const bool vec = (w % 16 == 0) && aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
                          (nv12 || (aligned(f.c1, ca) && f.sc1 % ca == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
         const bool bulk = vec && bps == 1 && (w % 32 == 0) && aligned(f.c0, 16) && f.sc0 % 16 == 0 && (nv12 || (aligned(f.c1, 16) && f.sc1 % 16 == 0));
         f.fast = bulk ? vep::PATH_BULK : vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;
-        if (vep::fmt_is_444(s.fmt)) f.fast = vep::PATH_GENERIC;   // 4:4:4 (rare from cameras) runs on the scalar path everywhere
-        // only the tick kernel has a vector path for 4:2:2 and for 10-bit samples
-        f.fast_tbl = (vep::fmt_is_422(s.fmt) || bps == 2) ? vep::PATH_GENERIC : f.fast;
+        if (vep::fmt_is_444(s.fmt)) f.fast = (f.fast != vep::PATH_GENERIC && homogeneous && vec444_ok) ? vep::PATH_VECTOR : vep::PATH_GENERIC;
+        // only the tick kernel has a vector path for 4:2:2, 4:4:4 and for 10-bit samples
+        f.fast_tbl = (vep::fmt_is_422(s.fmt) || vep::fmt_is_444(s.fmt) || bps == 2) ? vep::PATH_GENERIC : f.fast;
         f.segs = (w + vep::kSegPx - 1) / vep::kSegPx;
         f.segs_magic = f.segs == 1 ? 0u : (uint32_t)((((uint64_t)1 << 32) + f.segs - 1) / f.segs);
         f.item_begin = t.total_items;
@@ -214,6 +218,9 @@ struct vep_ctx {
     std::vector<uint8_t> tick_blob;
 };
 
+// 4:4:4 frames may take the vector path only where a format-specialised tick kernel will run them
+static inline bool vec444_ok(const vep_ctx *c) { return c->kernel == 2 && c->specialize && c->rpt == 2 && c->minb == 4; }
+
 struct vep_plan {
     vep_ctx *ctx = nullptr;
     FrameDev *d_frames = nullptr;
@@ -275,6 +282,8 @@ static const void *tick_kernel(int rpt, int minb, int only_fmt) {
             case VEP_FMT_YUV422P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_YUV422P>;
             case VEP_FMT_YUVJ422P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_YUVJ422P>;
             case VEP_FMT_YUV420P10LE: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 3, vep::FMT_YUV420P10>;   // 80 registers: no spills
+            case VEP_FMT_YUV444P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 3, vep::FMT_YUV444P>;
+            case VEP_FMT_YUVJ444P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 3, vep::FMT_YUVJ444P>;
             default: break;
         }
     }
@@ -426,7 +435,7 @@ extern "C" int vep_convert_batch(vep_ctx *c, const vep_frame_desc *descs, int n,
     if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
     DeviceGuard g(c->device);
     std::lock_guard<std::mutex> lk(c->mu);
-    int rc = build_tables(descs, n, c->scratch, c->rpt);
+    int rc = build_tables(descs, n, c->scratch, c->rpt, vec444_ok(c));
     if (rc) return rc;
     rc = upload_and_launch(c, c->scratch, (cudaStream_t)cuda_stream);
     if (rc) return rc;
@@ -439,7 +448,7 @@ extern "C" int vep_plan_create(vep_ctx *c, const vep_frame_desc *descs, int n, v
     *out = nullptr;
     DeviceGuard g(c->device);
     Tables t;
-    int rc = build_tables(descs, n, t, c->rpt);
+    int rc = build_tables(descs, n, t, c->rpt, vec444_ok(c));
     if (rc) return rc;
     vep_plan *p = new (std::nothrow) vep_plan();
     if (!p) return fail(VEP_ERR_NOMEM, "out of host memory");
@@ -814,7 +823,7 @@ static int tick_enqueue(vep_ctx *c, TickRec &t, int *n_frames) {
     }
     if (t.slots.empty()) return VEP_OK;
     // 2. one batched launch for the whole tick
-    int rc = build_tables(descs.data(), (int)descs.size(), c->scratch, c->rpt);
+    int rc = build_tables(descs.data(), (int)descs.size(), c->scratch, c->rpt, vec444_ok(c));
     if (rc) return rc;
     CUDA_TRY(cudaEventRecord(t.k0, c->main));
     rc = upload_and_launch(c, c->scratch, c->main);

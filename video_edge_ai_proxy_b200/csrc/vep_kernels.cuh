@@ -128,6 +128,17 @@ __device__ __forceinline__ ChromaPair chroma_a_sum2(uint32_t su, uint32_t sv) {
                        (int)su * (M::gu_mul / 2) + M::gu_add, (int)sv * (M::gv_mul / 2) + M::gv_add);
 }
 
+// channel pairs [c0,0,c1,0] of pixels (0,1) and (2,3) -> the 12 bytes B0 G0 R0 B1 | G1 R1 B2 G2 | R2 B3 G3 R3
+__device__ __forceinline__ void interleave_bgr(uint32_t bp, uint32_t gp, uint32_t rp, uint32_t bq, uint32_t gq, uint32_t rq,
+                                               uint32_t &w0, uint32_t &w1, uint32_t &w2) {
+    const uint32_t bgp = gp * 256u + bp;   // [B0 G0 B1 G1]
+    const uint32_t bgq = gq * 256u + bq;   // [B2 G2 B3 G3]
+    w0 = prmt(bgp, rp, 0x2410);            // B0 G0 R0 B1
+    const uint32_t x = prmt(bgp, rp, 0x0063);   // G1 R1 . .
+    w1 = prmt(x, bgq, 0x5410);             // G1 R1 B2 G2
+    w2 = prmt(bgq, rq, 0x6324);            // R2 B3 G3 R3
+}
+
 // four luma IMAD results (upper halves = y - 1024) + the two chroma pairs covering them -> 12 output bytes
 __device__ __forceinline__ void pack4_a(int t0, int t1, int t2, int t3, const ChromaPair &P, const ChromaPair &Q,
                                         uint32_t &w0, uint32_t &w1, uint32_t &w2) {
@@ -135,12 +146,7 @@ __device__ __forceinline__ void pack4_a(int t0, int t1, int t2, int t3, const Ch
     const uint32_t yq = prmt((uint32_t)t2, (uint32_t)t3, 0x7632);
     const uint32_t bp = add_sat_u8_x2(yp, P.cb2), gp = add_sat_u8_x2(yp, P.cg2), rp = add_sat_u8_x2(yp, P.cr2);
     const uint32_t bq = add_sat_u8_x2(yq, Q.cb2), gq = add_sat_u8_x2(yq, Q.cg2), rq = add_sat_u8_x2(yq, Q.cr2);
-    const uint32_t bgp = gp * 256u + bp;   // [B0 G0 B1 G1]
-    const uint32_t bgq = gq * 256u + bq;   // [B2 G2 B3 G3]
-    w0 = prmt(bgp, rp, 0x2410);            // B0 G0 R0 B1
-    const uint32_t x = prmt(bgp, rp, 0x0063);   // G1 R1 . .
-    w1 = prmt(x, bgq, 0x5410);             // G1 R1 B2 G2
-    w2 = prmt(bgq, rq, 0x6324);            // R2 B3 G3 R3
+    interleave_bgr(bp, gp, rp, bq, gq, rq, w0, w1, w2);
 }
 
 // 4 luma samples (one 32-bit word) + the two chroma pairs covering them -> 12 output bytes
@@ -232,6 +238,32 @@ __device__ __forceinline__ void compute_p10(const uint4 &ya_lo, const uint4 &ya_
 }
 
 
+
+// ---- 4:4:4, one row of 16 px: swscale's full-chroma C stage (one rounding per channel, wrapping 32-bit sums) ----
+template <bool FULL>
+__device__ __forceinline__ void compute_444_row(const uint4 &y, const uint4 &u, const uint4 &v, uint32_t (&o)[12]) {
+    using K = KA<FULL>;
+    constexpr uint32_t yC9 = (uint32_t)K::yC << 9;
+    constexpr uint32_t kB = (uint32_t)(-(K::yOff << 6) * K::yC + (1 << 21)) - 128u * ((uint32_t)K::ub << 9);
+    constexpr uint32_t kR = (uint32_t)(-(K::yOff << 6) * K::yC + (1 << 21)) - 128u * ((uint32_t)K::vr << 9);
+    constexpr uint32_t kG = (uint32_t)(-(K::yOff << 6) * K::yC + (1 << 21)) - 128u * ((uint32_t)(K::ug << 9)) - 128u * ((uint32_t)(K::vg << 9));
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        const uint32_t yw = word_of(y, g), uw = word_of(u, g), vw = word_of(v, g);
+        int b[4], gg[4], r[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t Y = i == 3 ? yw >> 24 : byte_of(yw, i), U = i == 3 ? uw >> 24 : byte_of(uw, i), V = i == 3 ? vw >> 24 : byte_of(vw, i);
+            const uint32_t yt = Y * yC9;
+            b[i] = (int)(yt + U * ((uint32_t)K::ub << 9) + kB) >> 22;
+            r[i] = (int)(yt + V * ((uint32_t)K::vr << 9) + kR) >> 22;
+            gg[i] = (int)(yt + U * (uint32_t)(K::ug << 9) + V * (uint32_t)(K::vg << 9) + kG) >> 22;
+        }
+        auto pair = [](int a, int c) { return __vimin_s16x2_relu(prmt((uint32_t)a, (uint32_t)c, 0x5410), 0x00ff00ffu); };   // values fit s16: |x>>22| <= 512
+        interleave_bgr(pair(b[0], b[1]), pair(gg[0], gg[1]), pair(r[0], r[1]), pair(b[2], b[3]), pair(gg[2], gg[3]), pair(r[2], r[3]),
+                       o[3 * g], o[3 * g + 1], o[3 * g + 2]);
+    }
+}
 
 // ---- one lane's 16 px x 2 rows, planar: uu/vv hold 8 chroma samples each ---------------------------
 template <bool FULL>
@@ -556,7 +588,7 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     const bool nv12 = fmt_is_semiplanar(fmt);
     const bool p10 = fmt == FMT_YUV420P10;               // 16-bit containers: loaded per row pair below, not here
     const int cshift = fmt_is_422(fmt) ? 1 : 0;           // 4:2:2: chroma row of luma row j is row j, not j/2
-    if (active && !p10) {
+    if (active && !p10 && !fmt_is_444(fmt)) {
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
             const int rp = min(rp0 + r, hp - 1);            // clamp: an odd tail group re-reads the last pair (not stored)
@@ -582,7 +614,20 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     for (int r = 0; r < RPT; ++r) {
         const int rp = rp0 + r;
         if (rp >= hp) break;                                // warp-uniform
-        if (active && p10) {
+        if (ONLY >= 0 && active && fmt_is_444(fmt)) {   // compiled into the 4:4:4 instantiations only (register pressure)
+            // 4:4:4: three full-resolution planes, one row at a time (park it, then the next)
+            uint32_t o[12];
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const size_t row = (size_t)(2 * rp + q);
+                const uint4 yy = ld_stream_v4(f.y + row * f.sy + x), uu4 = ld_stream_v4(f.c0 + row * f.sc0 + x), vv4 = ld_stream_v4(f.c1 + row * f.sc1 + x);
+                if (fmt == FMT_YUV444P) compute_444_row<false>(yy, uu4, vv4, o);
+                else compute_444_row<true>(yy, uu4, vv4, o);
+                uint8_t *t = q ? t1 : t0;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) *reinterpret_cast<uint4 *>(t + lane * 48 + k * 16) = make_uint4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
+            }
+        } else if (active && p10) {
             // 10-bit: 32 B of luma per row and lane, 16 B per chroma plane; the row above feeds the even row
             const uint8_t *yr = f.y + (size_t)(2 * rp) * f.sy + 2 * x;
             const uint4 a_lo = ld_stream_v4(yr), a_hi = ld_stream_v4(yr + 16), b_lo = ld_stream_v4(yr + f.sy), b_hi = ld_stream_v4(yr + f.sy + 16);
