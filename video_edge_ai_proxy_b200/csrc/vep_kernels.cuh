@@ -1,16 +1,21 @@
-// vep_kernels.cuh — sm_100a kernels: batched YUV 4:2:0 -> BGR24 (planar limited/full range, NV12).
+// vep_kernels.cuh — sm_100a kernels: batched YUV -> BGR24 (planar 4:2:0 / 4:2:2 / 4:4:4 limited and full
+// range, NV12 / NV21, 10-bit 4:2:0).
 //
 // Takes over the arithmetic of reference python/read_image.py:94 (`frame.to_ndarray('bgr24')`,
 // i.e. PyAV -> libswscale `sws_scale`).  Results are bit-exact with libswscale's default x86
-// path; the closed forms are restated in oracle/formulas.py (formulas A, B, C) and DESIGN.md.
+// path; the closed forms are restated in oracle/formulas.py and DESIGN.md.
 //
 // Shape of the work (HBM-bound byte arithmetic, no tensor cores): one launch covers every frame
-// of a tick.  A CTA looks up (frame, first item) in a per-CTA work table; each of its 8 warps
-// converts one "item" = 2 luma rows x 512 px.  A lane owns 16 px of both rows: two 16-byte Y
-// loads, one 8-byte U and one 8-byte V load (NV12: two 16-byte UV loads), so every chroma sample
-// is fetched once for its 2x2 luma block.  The 96 output bytes per lane are re-ordered through a
+// of a tick.  Each warp converts "items" = 2 luma rows x 512 px.  A lane owns 16 px of both rows: two
+// 16-byte Y loads, one 8-byte U and one 8-byte V load (NV12: two 16-byte UV loads), so every chroma
+// sample is fetched once for its 2x2 luma block.  The 96 output bytes per lane are re-ordered through a
 // per-warp shared-memory tile so that global stores are 16 bytes per lane and contiguous across
 // the warp (3-byte pixels would otherwise scatter 48-byte strided pieces).
+//
+// Three kernels, in file order: yuv_to_bgr24_batched (device tables; fallback beyond 128 frames and
+// the store-mode experiments), yuv_to_bgr24_tick (the DEFAULT: descriptor table in kernel parameters,
+// programmatic dependent launch, per-format instantiations), yuv_to_bgr24_persistent (per-warp TMA
+// pipelines; kept as a measured alternative, slower).  DESIGN.md section 4 has the numbers.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -516,7 +521,7 @@ yuv_to_bgr24_batched(const FrameDev *__restrict__ frames, const CtaWork *__restr
 
 
 // ================================================================================================
-// Tick kernel (the default): descriptor table in the kernel-parameter constant bank.
+// Tick kernel (THE DEFAULT): descriptor table in the kernel-parameter constant bank.
 //
 // Same tiling as the table-driven kernel above (one warp = 512 px x 2 luma rows per row pair,
 // shared-memory re-order, 16-byte warp-contiguous stores) but nothing on a CTA's critical path
@@ -683,7 +688,7 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
 }
 
 // ================================================================================================
-// Persistent, TMA-pipelined kernel (the default).
+// Persistent, TMA-pipelined kernel (alternative, VEP_KERNEL=persistent; measured slower than the tick kernel).
 //
 // Item space: every frame contributes items (bulk/vector path: one item = 2 luma rows x 512 px;
 // generic path: one item = 1024 2x2 blocks); FrameDev::item_begin is the running prefix, with a
