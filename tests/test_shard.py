@@ -61,3 +61,24 @@ def test_world_size_2_gloo_sharding(tmp_path):
                          capture_output=True, text=True, env=env, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "GLOO_OK" in out.stdout
+
+
+def test_bench_schedules_match_the_baseline_configs():
+    import numpy as np
+    sys.path.insert(0, ROOT)
+    import bench
+    # key-frame-only: GOP 30, every camera converts exactly once per 30 ticks, phases staggered
+    s = bench.schedule_for("8x4k-nv12-keyframe", 8)
+    assert len(s) == 30 and sorted(c for t in s for c in t) == list(range(8)) and max(len(t) for t in s) == 1
+    # interval skip: seeded Bernoulli(0.25) per camera per tick, seed = tick index
+    s = bench.schedule_for("mixed128-skip", 128)
+    assert len(s) == 16
+    for t, sel in enumerate(s):
+        assert sel == [int(c) for c in np.nonzero(np.random.default_rng(t).random(128) < 0.25)[0]]
+    assert 0.2 < sum(len(t) for t in s) / (16 * 128) < 0.3
+    cams = bench.cameras_for_rank("mixed128-skip", 0, 1)
+    assert [(c["w"], c["h"]) for c in cams].count((1920, 1080)) == 42 and len(cams) == 128
+    # default: every camera every tick; ranks own disjoint cameras
+    assert bench.schedule_for("16x1080p", 16) == [list(range(16))]
+    a, b = bench.cameras_for_rank("16x1080p", 0, 2), bench.cameras_for_rank("16x1080p", 1, 2)
+    assert {c["camera"] for c in a}.isdisjoint({c["camera"] for c in b}) and len(a) == len(b) == 16
