@@ -384,3 +384,31 @@ def test_random_geometry_fuzz_one_launch_per_round(path):
             rows = o[off:off + h * dstride].reshape(h, dstride)
             assert np.array_equal(rows[:, :3 * w].reshape(h, w, 3), F.to_bgr24(fmt, planes)), (rnd, fmt, w, h, pad, off)
             assert (rows[:, 3 * w:] == 0x5A).all() and (o[:off] == 0x5A).all() and (o[off + h * dstride:] == 0x5A).all(), (rnd, fmt, w, h, pad, off)
+
+
+@pytest.mark.parametrize("fmt", ALL_FORMATS)
+def test_known_answer_frames_and_video_legal_levels(path, fmt):
+    """SURVEY §8(d) value distributions beyond uniform noise: all-0, all-max, a gray ramp with neutral chroma,
+    and video-legal levels — each against the oracle, on a vector-path size and a ragged one."""
+    ten = fmt == "yuv420p10le"
+    top, mid = (1023, 512) if ten else (255, 128)
+    for w, h in ((1040, 16), (50, 10)):
+        ref = make_planes(fmt, w, h, 0)
+        for kind in ("zero", "max", "ramp"):
+            planes = []
+            for i, p in enumerate(ref):
+                if kind == "zero":
+                    a = np.zeros_like(p)
+                elif kind == "max":
+                    a = np.full_like(p, top)
+                elif i == 0:
+                    a = (np.arange(p.shape[1], dtype=np.int64)[None, :] * (top + 1) // p.shape[1] + np.zeros((p.shape[0], 1), np.int64)).astype(p.dtype)
+                else:
+                    a = np.full_like(p, mid)
+                planes.append(a)
+            got = gpu_convert(path, fmt, planes)
+            assert np.array_equal(got, F.to_bgr24(fmt, planes)), (fmt, w, h, kind)
+            if kind == "ramp" and fmt not in ("yuv444p", "yuvj444p", "yuv420p10le"):
+                assert (got[..., 0] == got[..., 1]).all() and (got[..., 1] == got[..., 2]).all()    # neutral chroma -> gray
+        legal = make_planes(fmt, w, h, 3, dist="video")
+        assert np.array_equal(gpu_convert(path, fmt, legal), F.to_bgr24(fmt, legal)), (fmt, w, h, "video")
