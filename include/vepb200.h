@@ -46,7 +46,8 @@ typedef enum {
     VEP_FMT_YUV420P10LE = 6, /* planar 4:2:0, 10-bit samples (<= 1023) in little-endian 16-bit containers, limited range
                                (HEVC Main10); strides in BYTES; height >= 8 */
     VEP_FMT_YUV444P = 7,   /* planar 4:4:4, limited range: chroma planes are W x H */
-    VEP_FMT_YUVJ444P = 8   /* planar 4:4:4, full range */
+    VEP_FMT_YUVJ444P = 8,  /* planar 4:4:4, full range */
+    VEP_FMT_GRAY8 = 9      /* luma only (monochrome decode): plane[0] only, B = G = R = Y as libswscale does */
 } vep_pixfmt;
 
 /* One frame of a batched conversion, all pointers in DEVICE memory.

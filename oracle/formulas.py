@@ -265,7 +265,14 @@ def yuv444p_to_bgr24(Y, U, V, full_range: bool = False) -> np.ndarray:
     return np.stack([fin(Yt + Uc * k["ub"]), fin(Yt + Uc * k["ug"] + Vc * k["vg"]), fin(Yt + Vc * k["vr"])], -1)
 
 
+def gray_to_bgr24(Y) -> np.ndarray:
+    """gray (monochrome decode): libswscale treats the plane as full-range luma and replicates it, B = G = R = Y (probed)."""
+    return np.repeat(Y[..., None], 3, axis=2)
+
+
 def to_bgr24(fmt: str, planes) -> np.ndarray:
+    if fmt == "gray":
+        return gray_to_bgr24(planes[0])
     if fmt == "yuv444p":
         return yuv444p_to_bgr24(planes[0], planes[1], planes[2], False)
     if fmt == "yuvj444p":

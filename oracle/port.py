@@ -42,6 +42,11 @@ def to_bgr24(fmt: str, planes) -> np.ndarray:
     planes = [np.ascontiguousarray(p) for p in planes]
     h, w = planes[0].shape
     out = np.empty((h, w, 3), np.uint8)
+    if fmt == "gray":                       # B = G = R = Y; nothing to restate in C
+        if w <= 0 or h <= 0 or w % 2 or h % 2:
+            raise ValueError(f"port rejected geometry {w}x{h} ({fmt})")
+        out[...] = planes[0][..., None]
+        return out
     if fmt in ("yuv420p", "yuvj420p"):
         Y, U, V = planes
         r = lib.port_yuv420p_to_bgr24(Y.ctypes.data, Y.strides[0], U.ctypes.data, U.strides[0],

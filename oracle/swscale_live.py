@@ -23,7 +23,7 @@ import threading
 import numpy as np
 
 # AVPixelFormat ids of the bundled FFmpeg (checked in `_load()` via av_get_pix_fmt).
-PIX_FMT = {"yuv420p": 0, "bgr24": 3, "yuv422p": 4, "yuv444p": 5, "yuvj420p": 12, "yuvj422p": 13, "yuvj444p": 14, "nv12": 23, "nv21": 24, "yuv420p10le": 62}
+PIX_FMT = {"gray": 8, "yuv420p": 0, "bgr24": 3, "yuv422p": 4, "yuv444p": 5, "yuvj420p": 12, "yuvj422p": 13, "yuvj444p": 14, "nv12": 23, "nv21": 24, "yuv420p10le": 62}
 SWS_BILINEAR = 2  # PyAV's default `interpolation` for VideoFrame.reformat
 
 # swscale's SIMD row loops run in 16/32-pixel steps and touch bytes past the visible row end
@@ -139,14 +139,17 @@ class Converter:
         full_c = fmt in ("yuv444p", "yuvj444p")
         ch = h if (full_c or fmt in ("yuv422p", "yuvj422p")) else h // 2
         self.cw = w if full_c else w // 2
-        if fmt in ("nv12", "nv21"):
+        if fmt == "gray":
+            self.c0 = self.c1 = None
+            self.s0 = 0
+        elif fmt in ("nv12", "nv21"):
             self.c0, self.s0, self._k0 = _padded(h // 2, w)
             self.c1 = None
         else:
             self.c0, self.s0, self._k0 = _padded(ch, self.cw * self.bps)
             self.c1, self.s1, self._k1 = _padded(ch, self.cw * self.bps)
         self.dst, self.sd, self._kd = _padded(h, w * 3)
-        self._src = (ctypes.c_void_p * 4)(self.y.ctypes.data, self.c0.ctypes.data,
+        self._src = (ctypes.c_void_p * 4)(self.y.ctypes.data, self.c0.ctypes.data if self.c0 is not None else None,
                                           self.c1.ctypes.data if self.c1 is not None else None,
                                           None)
         self._sstr = (ctypes.c_int * 4)(self.sy, self.s0,
@@ -166,6 +169,8 @@ class Converter:
         w, h = self.w, self.h
         as_bytes = lambda p: np.ascontiguousarray(p).view(np.uint8).reshape(p.shape[0], -1)   # u16 samples -> LE bytes
         self.y[:, :w * self.bps] = as_bytes(planes[0])
+        if self.fmt == "gray":
+            return
         if self.fmt in ("nv12", "nv21"):
             self.c0[:, :w] = planes[1]
         else:

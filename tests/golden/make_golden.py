@@ -45,7 +45,7 @@ EXTRA = [  # more rows (simd path), sizes/seeds the parity tests use
     # formats beyond SURVEY's three (probed: 4:2:2 keeps every chroma row; nv21 = nv12 with V first)
     ("yuvj422p", 1920, 1080, 0), ("yuv422p", 640, 480, 1), ("nv21", 1280, 720, 0), ("yuvj422p", 50, 6, 2), ("nv21", 642, 10, 3),
     ("yuv420p10le", 1920, 1080, 0), ("yuv420p10le", 642, 10, 1), ("yuv420p10le", 3840, 2160, 2),
-    ("yuv444p", 1920, 1080, 0), ("yuvj444p", 1280, 720, 1), ("yuv444p", 50, 6, 2),
+    ("yuv444p", 1920, 1080, 0), ("yuvj444p", 1280, 720, 1), ("yuv444p", 50, 6, 2), ("gray", 1280, 720, 0), ("gray", 50, 6, 1),
 ]
 
 SMALL = [  # stored raw (inputs + outputs) so the oracle can be checked without libswscale

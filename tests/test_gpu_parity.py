@@ -62,7 +62,7 @@ def test_exhaustive_yuv_triples_planar_both_ranges(path):
             assert np.array_equal(got[r0:r0 + 512], want), (fmt, r0)
 
 
-ALL_FORMATS = ["yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le", "yuv444p", "yuvj444p"]
+ALL_FORMATS = ["yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le", "yuv444p", "yuvj444p", "gray"]
 TALL_ONLY = ("nv12", "nv21", "yuv420p10le")     # formats whose rule needs H >= 8
 
 
@@ -98,7 +98,7 @@ def test_live_libswscale_agrees_on_the_box(path):
     assert L.on_simd_path()
     for fmt, w, h in (("yuv420p", 1920, 1080), ("yuvj420p", 640, 480), ("nv12", 1280, 720), ("yuv420p", 50, 6),
                       ("nv21", 1920, 1080), ("yuv422p", 1280, 720), ("yuvj422p", 1920, 1080), ("yuvj422p", 50, 6),
-                      ("yuv420p10le", 1920, 1080), ("yuv420p10le", 50, 10), ("yuv444p", 1920, 1080), ("yuvj444p", 50, 6)):
+                      ("yuv420p10le", 1920, 1080), ("yuv420p10le", 50, 10), ("yuv444p", 1920, 1080), ("yuvj444p", 50, 6), ("gray", 1920, 1080), ("gray", 50, 6)):
         planes = make_planes(fmt, w, h, 77)
         assert np.array_equal(gpu_convert(path, fmt, planes), L.to_bgr24(fmt, planes, w, h)), (fmt, w, h)
 
@@ -250,7 +250,7 @@ def test_tick_kernel_variants_bit_identical(env, small_frames):
             descs, keep = [], []
             for i in range(n):
                 fmt, w, h = (("yuv420p", 320, 240), ("nv12", 352, 288), ("yuvj420p", 160, 120), ("yuv420p", 50, 6),
-                             ("yuvj422p", 320, 240), ("nv21", 64, 48), ("yuv420p10le", 160, 120), ("yuvj444p", 96, 64))[i % 8]
+                             ("yuvj422p", 320, 240), ("nv21", 64, 48), ("yuv420p10le", 160, 120), ("yuvj444p", 96, 64), ("gray", 64, 32))[i % 9]
                 planes = make_planes(fmt, w, h, i)
                 t = [torch.from_numpy(q).cuda() for q in planes]
                 out = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
@@ -329,7 +329,7 @@ def test_rejections(path):
     good = desc_from_tensors("yuv420p", t, out)
     for mutate, status in ((lambda d: setattr(d, "width", 63), _abi.VEP_ERR_GEOMETRY),
                            (lambda d: setattr(d, "height", 15), _abi.VEP_ERR_GEOMETRY),
-                           (lambda d: setattr(d, "fmt", 9), _abi.VEP_ERR_INVALID_ARG),
+                           (lambda d: setattr(d, "fmt", 99), _abi.VEP_ERR_INVALID_ARG),
                            (lambda d: setattr(d, "dst_stride", 100), _abi.VEP_ERR_GEOMETRY),
                            (lambda d: setattr(d, "dst", 0), _abi.VEP_ERR_INVALID_ARG)):
         d = desc_from_tensors("yuv420p", t, out)
@@ -408,7 +408,7 @@ def test_known_answer_frames_and_video_legal_levels(path, fmt):
                 planes.append(a)
             got = gpu_convert(path, fmt, planes)
             assert np.array_equal(got, F.to_bgr24(fmt, planes)), (fmt, w, h, kind)
-            if kind == "ramp" and fmt not in ("yuv444p", "yuvj444p", "yuv420p10le"):
+            if kind == "ramp" and fmt not in ("yuv444p", "yuvj444p", "yuv420p10le"):   # (those round per channel / differ in the tail rows)
                 assert (got[..., 0] == got[..., 1]).all() and (got[..., 1] == got[..., 2]).all()    # neutral chroma -> gray
         legal = make_planes(fmt, w, h, 3, dist="video")
         assert np.array_equal(gpu_convert(path, fmt, legal), F.to_bgr24(fmt, legal)), (fmt, w, h, "video")

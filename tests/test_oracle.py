@@ -41,7 +41,7 @@ def test_small_fixtures_numpy_and_c_port(small_frames):
         assert np.array_equal(P.to_bgr24(fmt, planes), out), (fmt, w, h)
 
 
-@pytest.mark.parametrize("row", range(38))
+@pytest.mark.parametrize("row", range(42))
 def test_numpy_restatement_matches_golden_table(golden_pixels, row):
     rows = golden_pixels["rows"]
     if row >= len(rows):
@@ -133,7 +133,7 @@ def test_live_library_reproduces_survey_checksums(golden_pixels, fmt, w, h, seed
 
 @needs_live
 def test_live_vs_restatement_ragged_widths_and_heights():
-    for fmt in ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le", "yuv444p", "yuvj444p"):
+    for fmt in ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le", "yuv444p", "yuvj444p", "gray"):
         for w in (2, 6, 14, 16, 18, 30, 34, 62, 130, 642):
             for h in (2, 4, 8, 10, 18):
                 if fmt in ("nv12", "nv21", "yuv420p10le") and h < 8:

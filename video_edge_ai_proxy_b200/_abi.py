@@ -13,7 +13,7 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libvepb200.so")
 
-VEP_FMT = {"yuv420p": 0, "yuvj420p": 1, "nv12": 2, "nv21": 3, "yuv422p": 4, "yuvj422p": 5, "yuv420p10le": 6, "yuv444p": 7, "yuvj444p": 8}
+VEP_FMT = {"yuv420p": 0, "yuvj420p": 1, "nv12": 2, "nv21": 3, "yuv422p": 4, "yuvj422p": 5, "yuv420p10le": 6, "yuv444p": 7, "yuvj444p": 8, "gray": 9}
 VEP_OK, VEP_ERR_INVALID_ARG, VEP_ERR_GEOMETRY, VEP_ERR_CUDA = 0, -1, -2, -3
 VEP_ERR_NOMEM, VEP_ERR_STATE, VEP_ERR_NO_FRAME, VEP_ERR_BUSY = -4, -5, -6, -7
 

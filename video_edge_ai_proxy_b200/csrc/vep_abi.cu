@@ -97,31 +97,33 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1, 
     for (int i = 0; i < n; ++i) {
         const vep_frame_desc &s = d[i];
         if (!s.convert) continue;
-        if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_YUVJ444P) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
+        if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_GRAY8) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
         const int w = s.width, h = s.height;
         if (w <= 0 || h <= 0 || w > kMaxDim || h > kMaxDim || (w & 1) || (h & 1))
             return fail(VEP_ERR_GEOMETRY, "desc %d: %dx%d — 4:2:0 needs even, positive dimensions <= %d", i, w, h, kMaxDim);
         const bool nv12 = vep::fmt_is_semiplanar(s.fmt);
         const int bps = vep::fmt_bytes_per_sample(s.fmt);
         if ((nv12 || bps == 2) && h < 8) return fail(VEP_ERR_GEOMETRY, "desc %d: nv12/nv21/10-bit height %d < 8 (swscale changes its vertical chroma filter there)", i, h);
-        if (!s.plane[0] || !s.plane[1] || (!nv12 && !s.plane[2]) || !s.dst) return fail(VEP_ERR_INVALID_ARG, "desc %d: null plane or dst", i);
+        const bool gray = s.fmt == VEP_FMT_GRAY8;
+        if (!s.plane[0] || (!gray && (!s.plane[1] || (!nv12 && !s.plane[2]))) || !s.dst) return fail(VEP_ERR_INVALID_ARG, "desc %d: null plane or dst", i);
         const int cw = ((nv12 || vep::fmt_is_444(s.fmt)) ? w : w / 2) * bps;
-        if (s.stride[0] < w * bps || s.stride[1] < cw || (!nv12 && s.stride[2] < cw) || s.dst_stride < 3 * w)
+        if (s.stride[0] < w * bps || (!gray && (s.stride[1] < cw || (!nv12 && s.stride[2] < cw))) || s.dst_stride < 3 * w)
             return fail(VEP_ERR_GEOMETRY, "desc %d: a stride is smaller than its row", i);
         if (bps == 2 && ((s.stride[0] | s.stride[1] | s.stride[2]) & 1 || !aligned(s.plane[0], 2) || !aligned(s.plane[1], 2) || !aligned(s.plane[2], 2)))
             return fail(VEP_ERR_GEOMETRY, "desc %d: 16-bit samples need 2-byte aligned planes and even strides", i);
         FrameDev f{};
-        f.y = s.plane[0]; f.c0 = s.plane[1]; f.c1 = nv12 ? nullptr : s.plane[2]; f.dst = s.dst;
-        f.sy = s.stride[0]; f.sc0 = s.stride[1]; f.sc1 = nv12 ? 0 : s.stride[2]; f.sd = s.dst_stride;
+        f.y = s.plane[0]; f.c0 = gray ? s.plane[0] : s.plane[1]; f.c1 = (nv12 || gray) ? nullptr : s.plane[2]; f.dst = s.dst;
+        f.sy = s.stride[0]; f.sc0 = gray ? s.stride[0] : s.stride[1]; f.sc1 = (nv12 || gray) ? 0 : s.stride[2]; f.sd = s.dst_stride;
         f.w = w; f.h = h; f.fmt = s.fmt;
         const size_t ca = (nv12 || bps == 2 || vep::fmt_is_444(s.fmt)) ? 16 : 8;
         const bool vec = (w % 16 == 0) && aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
-                         (nv12 || (aligned(f.c1, ca) && f.sc1 % ca == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
+                         (nv12 || gray || (aligned(f.c1, ca) && f.sc1 % ca == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
         const bool bulk = vec && bps == 1 && (w % 32 == 0) && aligned(f.c0, 16) && f.sc0 % 16 == 0 && (nv12 || (aligned(f.c1, 16) && f.sc1 % 16 == 0));
         f.fast = bulk ? vep::PATH_BULK : vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;
-        if (vep::fmt_is_444(s.fmt)) f.fast = (f.fast != vep::PATH_GENERIC && homogeneous && vec444_ok) ? vep::PATH_VECTOR : vep::PATH_GENERIC;
-        // only the tick kernel has a vector path for 4:2:2, 4:4:4 and for 10-bit samples
-        f.fast_tbl = (vep::fmt_is_422(s.fmt) || vep::fmt_is_444(s.fmt) || bps == 2) ? vep::PATH_GENERIC : f.fast;
+        if (vep::fmt_vector_only_when_specialised(s.fmt))
+            f.fast = (f.fast != vep::PATH_GENERIC && homogeneous && vec444_ok) ? vep::PATH_VECTOR : vep::PATH_GENERIC;
+        // only the tick kernel has a vector path for 4:2:2, 4:4:4, gray and for 10-bit samples
+        f.fast_tbl = (vep::fmt_is_422(s.fmt) || vep::fmt_vector_only_when_specialised(s.fmt) || bps == 2) ? vep::PATH_GENERIC : f.fast;
         f.segs = (w + vep::kSegPx - 1) / vep::kSegPx;
         f.segs_magic = f.segs == 1 ? 0u : (uint32_t)((((uint64_t)1 << 32) + f.segs - 1) / f.segs);
         f.item_begin = t.total_items;
@@ -141,8 +143,8 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1, 
         }
         if ((int64_t)t.total_items + items > (int64_t)1 << 30) return fail(VEP_ERR_INVALID_ARG, "batch too large");
         t.total_items += items;
-        t.alg_bytes += vep::fmt_is_422(s.fmt) ? (int64_t)w * h * 5 : (bps == 2 || vep::fmt_is_444(s.fmt)) ? (int64_t)w * h * 6
-                                              : (int64_t)w * h * 9 / 2;   // read: 4:2:0 1.5, 4:2:2 2, 10-bit / 4:4:4 3 B/px
+        t.alg_bytes += gray ? (int64_t)w * h * 4 : vep::fmt_is_422(s.fmt) ? (int64_t)w * h * 5 : (bps == 2 || vep::fmt_is_444(s.fmt)) ? (int64_t)w * h * 6
+                                              : (int64_t)w * h * 9 / 2;   // read: gray 1, 4:2:0 1.5, 4:2:2 2, 10-bit / 4:4:4 3 B/px
         t.n_converted++;
     }
     FrameDev sentinel{};
@@ -284,6 +286,7 @@ static const void *tick_kernel(int rpt, int minb, int only_fmt) {
             case VEP_FMT_YUV420P10LE: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 3, vep::FMT_YUV420P10>;   // 80 registers: no spills
             case VEP_FMT_YUV444P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 3, vep::FMT_YUV444P>;
             case VEP_FMT_YUVJ444P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 3, vep::FMT_YUVJ444P>;
+            case VEP_FMT_GRAY8: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_GRAY8>;
             default: break;
         }
     }
@@ -578,7 +581,7 @@ static Stream *find_stream(vep_ctx *c, int id) {
 
 extern "C" int vep_stream_open(vep_ctx *c, int stream_id, int fmt, int w, int h, int ring_depth) {
     if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
-    if (fmt < VEP_FMT_YUV420P || fmt > VEP_FMT_YUVJ444P) return fail(VEP_ERR_INVALID_ARG, "unknown fmt %d", fmt);
+    if (fmt < VEP_FMT_YUV420P || fmt > VEP_FMT_GRAY8) return fail(VEP_ERR_INVALID_ARG, "unknown fmt %d", fmt);
     if (w <= 0 || h <= 0 || w > kMaxDim || h > kMaxDim || (w & 1) || (h & 1)) return fail(VEP_ERR_GEOMETRY, "%dx%d: need even, positive dimensions", w, h);
     if ((vep::fmt_is_semiplanar(fmt) || vep::fmt_bytes_per_sample(fmt) == 2) && h < 8) return fail(VEP_ERR_GEOMETRY, "nv12/nv21/10-bit height %d < 8", h);
     if (ring_depth < 1) ring_depth = 1;
@@ -595,7 +598,8 @@ extern "C" int vep_stream_open(vep_ctx *c, int stream_id, int fmt, int w, int h,
     const size_t ysz = (size_t)w * h * bps;       // bytes of the luma plane (chroma planes scale with it)
     s->off_c0 = align_up(ysz, 256);
     const size_t csz = vep::fmt_is_444(fmt) ? ysz : vep::fmt_is_422(fmt) ? ysz / 2 : ysz / 4;   // bytes of one planar chroma plane
-    if (vep::fmt_is_semiplanar(fmt)) { s->off_c1 = 0; s->in_bytes = s->off_c0 + ysz / 2; }
+    if (fmt == VEP_FMT_GRAY8) { s->off_c0 = s->off_c1 = 0; s->in_bytes = ysz; }
+    else if (vep::fmt_is_semiplanar(fmt)) { s->off_c1 = 0; s->in_bytes = s->off_c0 + ysz / 2; }
     else { s->off_c1 = s->off_c0 + align_up(csz, 256); s->in_bytes = s->off_c1 + csz; }
     s->out_bytes = (size_t)w * h * 3;
     s->in_slot = align_up(s->in_bytes, 4096);
@@ -665,6 +669,7 @@ static void plane_ptrs(Stream *s, uint8_t *base, uint8_t *pl[3], int32_t st[3]) 
     const int cwp = vep::fmt_is_444(s->fmt) ? s->w : s->w / 2;     // planar chroma samples per row
     pl[0] = base; pl[1] = base + s->off_c0; pl[2] = semi ? nullptr : base + s->off_c1;
     st[0] = s->w * bps; st[1] = semi ? s->w : cwp * bps; st[2] = semi ? 0 : cwp * bps;
+    if (s->fmt == VEP_FMT_GRAY8) { pl[1] = pl[2] = nullptr; st[1] = st[2] = 0; }
 }
 
 extern "C" int vep_acquire_input(vep_ctx *c, int stream_id, uint8_t *plane_out[3], int32_t stride_out[3]) {
@@ -730,12 +735,12 @@ extern "C" int vep_submit(vep_ctx *c, int stream_id, const uint8_t *const plane[
         __atomic_add_fetch(&c->stats.frames_offered, 1, __ATOMIC_RELAXED);
         return VEP_OK;
     }
-    const bool semi = vep::fmt_is_semiplanar(s->fmt);
-    if (!plane || !stride || !plane[0] || !plane[1] || (!semi && !plane[2])) return fail(VEP_ERR_INVALID_ARG, "null plane");
+    const bool semi = vep::fmt_is_semiplanar(s->fmt), gray = s->fmt == VEP_FMT_GRAY8;
+    if (!plane || !stride || !plane[0] || (!gray && (!plane[1] || (!semi && !plane[2])))) return fail(VEP_ERR_INVALID_ARG, "null plane");
     const int bps = vep::fmt_bytes_per_sample(s->fmt);
     const int cw = ((semi || vep::fmt_is_444(s->fmt)) ? s->w : s->w / 2) * bps;      // chroma row bytes
     const int crows = (vep::fmt_is_422(s->fmt) || vep::fmt_is_444(s->fmt)) ? s->h : s->h / 2;
-    if (stride[0] < s->w * bps || stride[1] < cw || (!semi && stride[2] < cw)) return fail(VEP_ERR_GEOMETRY, "stride smaller than row");
+    if (stride[0] < s->w * bps || (!gray && (stride[1] < cw || (!semi && stride[2] < cw)))) return fail(VEP_ERR_GEOMETRY, "stride smaller than row");
     uint8_t *pl[3];
     int32_t st[3];
     {
@@ -746,8 +751,8 @@ extern "C" int vep_submit(vep_ctx *c, int stream_id, const uint8_t *const plane[
     }
     // the copy runs outside the lock: one producer per stream
     copy_plane(pl[0], st[0], plane[0], stride[0], s->w * bps, s->h);
-    copy_plane(pl[1], st[1], plane[1], stride[1], cw, crows);
-    if (!semi) copy_plane(pl[2], st[2], plane[2], stride[2], cw, crows);
+    if (!gray) copy_plane(pl[1], st[1], plane[1], stride[1], cw, crows);
+    if (!semi && !gray) copy_plane(pl[2], st[2], plane[2], stride[2], cw, crows);
     return vep_commit_input(c, stream_id, meta);
 }
 
@@ -808,6 +813,7 @@ static int tick_enqueue(vep_ctx *c, TickRec &t, int *n_frames) {
             d.plane[0] = sl.d_in; d.plane[1] = sl.d_in + s->off_c0; d.plane[2] = semi ? nullptr : sl.d_in + s->off_c1;
             const int cwp = vep::fmt_is_444(s->fmt) ? s->w : s->w / 2;
             d.stride[0] = s->w * bps; d.stride[1] = semi ? s->w : cwp * bps; d.stride[2] = semi ? 0 : cwp * bps;
+            if (s->fmt == VEP_FMT_GRAY8) { d.plane[1] = d.plane[2] = nullptr; d.stride[1] = d.stride[2] = 0; }
             d.dst = sl.d_out; d.dst_stride = 3 * s->w; d.width = s->w; d.height = s->h; d.fmt = s->fmt; d.convert = 1;
             descs.push_back(d);
             write_framing(s, sl);
@@ -961,28 +967,29 @@ static CtaWork g_noalloc_h_work[VEP_NOALLOC_MAX_CTAS];
 
 // Validation + table row for one descriptor; mirrors build_tables() without touching the heap.
 static int noalloc_frame(const vep_frame_desc &s, int i, FrameDev &f) {
-    if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_YUVJ444P) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
+    if (s.fmt < VEP_FMT_YUV420P || s.fmt > VEP_FMT_GRAY8) return fail(VEP_ERR_INVALID_ARG, "desc %d: unknown fmt %d", i, s.fmt);
     const int w = s.width, h = s.height;
     if (w <= 0 || h <= 0 || w > kMaxDim || h > kMaxDim || (w & 1) || (h & 1))
         return fail(VEP_ERR_GEOMETRY, "desc %d: %dx%d — 4:2:0 needs even, positive dimensions <= %d", i, w, h, kMaxDim);
     const bool nv12 = vep::fmt_is_semiplanar(s.fmt);
     const int bps = vep::fmt_bytes_per_sample(s.fmt);
     if ((nv12 || bps == 2) && h < 8) return fail(VEP_ERR_GEOMETRY, "desc %d: nv12/nv21/10-bit height %d < 8", i, h);
-    if (!s.plane[0] || !s.plane[1] || (!nv12 && !s.plane[2]) || !s.dst) return fail(VEP_ERR_INVALID_ARG, "desc %d: null plane or dst", i);
+    const bool gray = s.fmt == VEP_FMT_GRAY8;
+    if (!s.plane[0] || (!gray && (!s.plane[1] || (!nv12 && !s.plane[2]))) || !s.dst) return fail(VEP_ERR_INVALID_ARG, "desc %d: null plane or dst", i);
     const int cw = ((nv12 || vep::fmt_is_444(s.fmt)) ? w : w / 2) * bps;
-    if (s.stride[0] < w * bps || s.stride[1] < cw || (!nv12 && s.stride[2] < cw) || s.dst_stride < 3 * w)
+    if (s.stride[0] < w * bps || (!gray && (s.stride[1] < cw || (!nv12 && s.stride[2] < cw))) || s.dst_stride < 3 * w)
         return fail(VEP_ERR_GEOMETRY, "desc %d: a stride is smaller than its row", i);
     if (bps == 2 && ((s.stride[0] | s.stride[1] | s.stride[2]) & 1 || !aligned(s.plane[0], 2) || !aligned(s.plane[1], 2) || !aligned(s.plane[2], 2)))
         return fail(VEP_ERR_GEOMETRY, "desc %d: 16-bit samples need 2-byte aligned planes and even strides", i);
     f = FrameDev{};
-    f.y = s.plane[0]; f.c0 = s.plane[1]; f.c1 = nv12 ? nullptr : s.plane[2]; f.dst = s.dst;
-    f.sy = s.stride[0]; f.sc0 = s.stride[1]; f.sc1 = nv12 ? 0 : s.stride[2]; f.sd = s.dst_stride;
+    f.y = s.plane[0]; f.c0 = gray ? s.plane[0] : s.plane[1]; f.c1 = (nv12 || gray) ? nullptr : s.plane[2]; f.dst = s.dst;
+    f.sy = s.stride[0]; f.sc0 = gray ? s.stride[0] : s.stride[1]; f.sc1 = (nv12 || gray) ? 0 : s.stride[2]; f.sd = s.dst_stride;
     f.w = w; f.h = h; f.fmt = s.fmt;
     const size_t ca = nv12 ? 16 : 8;
     const bool vec = (w % 16 == 0) && aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
-                     (nv12 || (aligned(f.c1, 8) && f.sc1 % 8 == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
+                     (nv12 || gray || (aligned(f.c1, 8) && f.sc1 % 8 == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
     f.fast = vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;   // the table-driven kernel knows these two paths
-    if (vep::fmt_is_422(s.fmt) || vep::fmt_is_444(s.fmt) || bps == 2) f.fast = vep::PATH_GENERIC;   // ... 4:2:2 / 4:4:4 / 10-bit on the scalar one
+    if (vep::fmt_is_422(s.fmt) || vep::fmt_vector_only_when_specialised(s.fmt) || bps == 2) f.fast = vep::PATH_GENERIC;   // ... 4:2:2 / 4:4:4 / gray / 10-bit on the scalar one
     f.fast_tbl = f.fast;
     f.segs = (w + vep::kSegPx - 1) / vep::kSegPx;
     return VEP_OK;

@@ -31,10 +31,12 @@ constexpr int kSegPx = 512;                       // pixels per warp item row (3
 constexpr int kSegBytes = kSegPx * 3;             // 1536 output bytes per row of an item
 constexpr int kGenericBlocksPerCta = 1024;        // 2x2 blocks per CTA on the generic path
 
-enum : int { FMT_YUV420P = 0, FMT_YUVJ420P = 1, FMT_NV12 = 2, FMT_NV21 = 3, FMT_YUV422P = 4, FMT_YUVJ422P = 5, FMT_YUV420P10 = 6, FMT_YUV444P = 7, FMT_YUVJ444P = 8 };
+enum : int { FMT_YUV420P = 0, FMT_YUVJ420P = 1, FMT_NV12 = 2, FMT_NV21 = 3, FMT_YUV422P = 4, FMT_YUVJ422P = 5, FMT_YUV420P10 = 6, FMT_YUV444P = 7, FMT_YUVJ444P = 8, FMT_GRAY8 = 9 };
 __host__ __device__ constexpr bool fmt_is_semiplanar(int f) { return f == FMT_NV12 || f == FMT_NV21; }
 __host__ __device__ constexpr bool fmt_is_422(int f) { return f == FMT_YUV422P || f == FMT_YUVJ422P; }
 __host__ __device__ constexpr bool fmt_is_444(int f) { return f == FMT_YUV444P || f == FMT_YUVJ444P; }
+// formats whose vector path is compiled into their own instantiation of the tick kernel only
+__host__ __device__ constexpr bool fmt_vector_only_when_specialised(int f) { return fmt_is_444(f) || f == FMT_GRAY8; }
 __host__ __device__ constexpr bool fmt_is_full_range(int f) { return f == FMT_YUVJ420P || f == FMT_YUVJ422P || f == FMT_YUVJ444P; }
 __host__ __device__ constexpr int fmt_bytes_per_sample(int f) { return f == FMT_YUV420P10 ? 2 : 1; }
 
@@ -407,6 +409,15 @@ __device__ __forceinline__ void generic_block_444(const FrameDev &f, int bx, int
 __device__ __forceinline__ void generic_block(const FrameDev &f, int bx, int by) {
     if (f.fmt == FMT_YUV420P10) { generic_block_p10(f, bx, by); return; }
     if (fmt_is_444(f.fmt)) { generic_block_444(f, bx, by); return; }
+    if (f.fmt == FMT_GRAY8) {   // monochrome decode: swscale replicates the (full-range) luma byte, B = G = R = Y
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            const uint8_t *y = f.y + (size_t)(2 * by + r) * f.sy + 2 * bx;
+            uint8_t *d = f.dst + (size_t)(2 * by + r) * f.sd + 6 * bx;
+            d[0] = d[1] = d[2] = y[0]; d[3] = d[4] = d[5] = y[1];
+        }
+        return;
+    }
     const uint8_t *y0 = f.y + (size_t)(2 * by) * f.sy + 2 * bx, *y1 = y0 + f.sy;
     uint8_t *d0 = f.dst + (size_t)(2 * by) * f.sd + 6 * bx, *d1 = d0 + f.sd;
     if (!fmt_is_semiplanar(f.fmt)) {
@@ -593,7 +604,7 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     const bool nv12 = fmt_is_semiplanar(fmt);
     const bool p10 = fmt == FMT_YUV420P10;               // 16-bit containers: loaded per row pair below, not here
     const int cshift = fmt_is_422(fmt) ? 1 : 0;           // 4:2:2: chroma row of luma row j is row j, not j/2
-    if (active && !p10 && !fmt_is_444(fmt)) {
+    if (active && !p10 && !fmt_vector_only_when_specialised(fmt)) {
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
             const int rp = min(rp0 + r, hp - 1);            // clamp: an odd tail group re-reads the last pair (not stored)
@@ -619,7 +630,21 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     for (int r = 0; r < RPT; ++r) {
         const int rp = rp0 + r;
         if (rp >= hp) break;                                // warp-uniform
-        if (ONLY >= 0 && active && fmt_is_444(fmt)) {   // compiled into the 4:4:4 instantiations only (register pressure)
+        if (ONLY >= 0 && active && fmt == FMT_GRAY8) {   // B = G = R = Y: three byte permutes per four pixels
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const uint4 yy = ld_stream_v4(f.y + (size_t)(2 * rp + q) * f.sy + x);
+                uint8_t *t = q ? t1 : t0;
+                uint32_t o[12];
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    const uint32_t yw = word_of(yy, g);
+                    o[3 * g] = prmt(yw, yw, 0x1000); o[3 * g + 1] = prmt(yw, yw, 0x2211); o[3 * g + 2] = prmt(yw, yw, 0x3332);
+                }
+#pragma unroll
+                for (int k = 0; k < 3; ++k) *reinterpret_cast<uint4 *>(t + lane * 48 + k * 16) = make_uint4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
+            }
+        } else if (ONLY >= 0 && active && fmt_is_444(fmt)) {   // compiled into the 4:4:4 instantiations only (register pressure)
             // 4:4:4: three full-resolution planes, one row at a time (park it, then the next)
             uint32_t o[12];
 #pragma unroll

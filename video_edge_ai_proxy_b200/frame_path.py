@@ -203,7 +203,7 @@ class FramePath:
         check(self._L.vep_acquire_input(self._ctx, self._sid(device_id), C.byref(ptrs), C.byref(strides)), "vep_acquire_input")
         ch = h if fmt in ("yuv422p", "yuvj422p", "yuv444p", "yuvj444p") else h // 2
         cw = w if fmt in ("yuv444p", "yuvj444p") else w // 2
-        shapes = [(h, w), (h // 2, w)] if fmt in ("nv12", "nv21") else [(h, w), (ch, cw), (ch, cw)]
+        shapes = [(h, w)] if fmt == "gray" else [(h, w), (h // 2, w)] if fmt in ("nv12", "nv21") else [(h, w), (ch, cw), (ch, cw)]
         out = []
         for i, shp in enumerate(shapes):
             buf = (C.c_uint8 * (shp[0] * strides[i])).from_address(ptrs[i])

@@ -25,7 +25,7 @@ from . import global_vars
 from .frame_path import FramePath, make_meta
 from .gate import DecodeGate
 
-_SUPPORTED = ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le", "yuv444p", "yuvj444p")
+_SUPPORTED = ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le", "yuv444p", "yuvj444p", "gray")
 
 
 def planes_of(frame):

@@ -8,7 +8,7 @@ from __future__ import annotations
 
 import numpy as np
 
-FORMATS = ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le", "yuv444p", "yuvj444p")
+FORMATS = ("yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p", "yuv420p10le", "yuv444p", "yuvj444p", "gray")
 
 
 def make_planes(fmt: str, w: int, h: int, seed: int, dist: str = "uniform"):
@@ -24,6 +24,8 @@ def make_planes(fmt: str, w: int, h: int, seed: int, dist: str = "uniform"):
         lo_y, hi_y, lo_c, hi_c = 16, 236, 16, 241
     else:
         raise ValueError(dist)
+    if fmt == "gray":             # monochrome decode: one full-range luma plane
+        return (rng.integers(lo_y, hi_y, (h, w), dtype=np.uint8),)
     if fmt == "yuv420p10le":      # 10-bit samples in little-endian 16-bit containers (HEVC Main10 decodes to this)
         s4 = lambda v: min(v * 4, 1024)
         Y = rng.integers(s4(lo_y), s4(hi_y), (h, w), dtype=np.uint16)
