@@ -416,6 +416,19 @@ def run_gpu(args):
     strict_ms = s0.elapsed_time(s1)
     strict_ms = max_over_ranks(strict_ms) if world > 1 else strict_ms
     strict_gbs = timed_bytes / (strict_ms / 1e3) / 1e9
+    # and with only the stores ordered after the previous tick (VEP_ORDER_WRITES: inputs do not come from the previous kernel)
+    o0, o1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    o0.record(stream)
+    for i in range(warm, warm + args.steps):
+        pl = plans[i % n_sets][i % n_pat]
+        if pl is not None:
+            pl.launch(sptr, order=1)
+    o1.record(stream)
+    torch.cuda.synchronize(dev)
+    ow_ms = o0.elapsed_time(o1)
+    ow_ms = max_over_ranks(ow_ms) if world > 1 else ow_ms
+    ow_gbs = timed_bytes / (ow_ms / 1e3) / 1e9
 
     for row in plans:
         for p in row:
@@ -520,7 +533,9 @@ def run_gpu(args):
                      "peak_source": peak_src, "frac_of_nominal_8TBs": round(achieved / 8000.0, 4),
                      "alg_bytes_per_launch": int(timed_bytes / max(gpu_launches, 1)),
                      "strict_stream_order": {"achieved": round(strict_gbs, 1), "frac": round(strict_gbs / peak, 4),
-                                             "frames_per_s": round(total_frames / (strict_ms / 1e3), 1)}, "kernel": {"persistent": "vep::yuv_to_bgr24_persistent", "oneshot": "vep::yuv_to_bgr24_batched"}.get(os.environ.get("VEP_KERNEL", "tick"), "vep::yuv_to_bgr24_tick")},
+                                             "frames_per_s": round(total_frames / (strict_ms / 1e3), 1)},
+                     "ordered_writes": {"achieved": round(ow_gbs, 1), "frac": round(ow_gbs / peak, 4),
+                                        "frames_per_s": round(total_frames / (ow_ms / 1e3), 1)}, "kernel": {"persistent": "vep::yuv_to_bgr24_persistent", "oneshot": "vep::yuv_to_bgr24_batched"}.get(os.environ.get("VEP_KERNEL", "tick"), "vep::yuv_to_bgr24_tick")},
         "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d_per_step), "d2h_bytes_per_step": int(d2h_per_step),
                 "steps": e2e_steps, "api": "FramePath.submit from one producer thread per camera (host planes -> pinned staging) + tick_begin/tick_wait (3 ticks in flight) + result_packed",
                 "pcie_gbs": round((h2d_per_step + d2h_per_step) * e2e_steps / e2e_s / 1e9, 2), "message_bytes": msg_bytes,

@@ -103,6 +103,17 @@ int vep_plan_launch(vep_plan *plan, void *cuda_stream);
  * then start this launch while the previous one is still draining; ordering against everything
  * else on the stream (copies, events, other kernels) is unchanged.  Results are identical. */
 int vep_plan_launch_overlapped(vep_plan *plan, void *cuda_stream);
+/* The general form.  `order` says what this launch must be ordered against with respect to the PREVIOUS KERNEL
+ * on the stream (copies, events and everything else keep ordinary stream order in all three):
+ *   VEP_ORDER_STRICT  everything (== vep_plan_launch): safe whatever the previous kernel did;
+ *   VEP_ORDER_WRITES  only this launch's stores wait for the previous kernel: valid when that kernel did not
+ *                     PRODUCE this launch's input planes (inputs that came from cudaMemcpy or from older work are
+ *                     fine) — consecutive ticks may then re-use one output buffer and the last one still wins;
+ *   VEP_ORDER_NONE    nothing (== vep_plan_launch_overlapped). */
+#define VEP_ORDER_STRICT 0
+#define VEP_ORDER_WRITES 1
+#define VEP_ORDER_NONE 2
+int vep_plan_launch_ordered(vep_plan *plan, void *cuda_stream, int order);
 /* frames with convert!=0, CTAs per launch, algorithmic bytes (4.5*W*H per converted frame) */
 int vep_plan_info(const vep_plan *plan, int *n_converted, int *n_ctas, int64_t *alg_bytes);
 void vep_plan_destroy(vep_plan *plan);

@@ -291,10 +291,15 @@ def test_overlapped_and_ordered_launches(path):
         t = [torch.from_numpy(q).cuda() for q in pl]
         keep.append((pl, t))
         plans.append(path.plan([desc_from_tensors("yuv420p", t, shared)]))
-    for pln in plans:
-        pln.launch(st)
-    torch.cuda.synchronize()
-    assert np.array_equal(shared.cpu().numpy(), F.to_bgr24("yuv420p", keep[-1][0]))
+    for order in (_abi.VEP_ORDER_STRICT, _abi.VEP_ORDER_WRITES):     # both keep write-after-write order
+        shared.zero_()
+        for _ in range(3):
+            for pln in plans:
+                pln.launch(st, order=order)
+        torch.cuda.synchronize()
+        assert np.array_equal(shared.cpu().numpy(), F.to_bgr24("yuv420p", keep[-1][0])), order
+    with pytest.raises(VepError):
+        plans[0].launch(st, order=7)
     for _, _, pln in sets:
         pln.close()
     for pln in plans:

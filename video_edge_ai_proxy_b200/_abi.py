@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libvepb200.so")
 
 VEP_FMT = {"yuv420p": 0, "yuvj420p": 1, "nv12": 2, "nv21": 3, "yuv422p": 4, "yuvj422p": 5, "yuv420p10le": 6, "yuv444p": 7, "yuvj444p": 8, "gray": 9}
 VEP_OK, VEP_ERR_INVALID_ARG, VEP_ERR_GEOMETRY, VEP_ERR_CUDA = 0, -1, -2, -3
+VEP_ORDER_STRICT, VEP_ORDER_WRITES, VEP_ORDER_NONE = 0, 1, 2
 VEP_ERR_NOMEM, VEP_ERR_STATE, VEP_ERR_NO_FRAME, VEP_ERR_BUSY = -4, -5, -6, -7
 
 
@@ -56,6 +57,7 @@ SIGNATURES = {
     "vep_plan_create": (_i, [_p, C.POINTER(FrameDesc), _i, _pp]),
     "vep_plan_launch": (_i, [_p, _p]),
     "vep_plan_launch_overlapped": (_i, [_p, _p]),
+    "vep_plan_launch_ordered": (_i, [_p, _p, _i]),
     "vep_plan_info": (_i, [_p, _ip, _ip, C.POINTER(C.c_int64)]),
     "vep_plan_destroy": (None, [_p]),
     "vep_stream_open": (_i, [_p, _i, _i, _i, _i, _i]),

@@ -228,7 +228,7 @@ struct vep_plan {
     FrameDev *d_frames = nullptr;
     CtaWork *d_work = nullptr;
     int n_ctas = 0, n_converted = 0, total_items = 0;
-    std::vector<uint8_t> tick_blob, tick_blob_overlap;   // TickParams<16|128> (wait_prior = 1 | 0), passed by value
+    std::vector<uint8_t> tick_blob, tick_blob_overlap, tick_blob_writes;   // TickParams<16|128>, wait_prior = 1 | 0 | 2, passed by value
     int tick_cap = 0, tick_grid = 0;
     int64_t alg_bytes = 0;
 };
@@ -465,6 +465,8 @@ extern "C" int vep_plan_create(vep_ctx *c, const vep_frame_desc *descs, int n, v
             p->n_ctas = p->tick_grid;
             p->tick_blob_overlap = p->tick_blob;
             reinterpret_cast<int32_t *>(p->tick_blob_overlap.data())[1] = 0;   // TickParams::wait_prior
+            p->tick_blob_writes = p->tick_blob;
+            reinterpret_cast<int32_t *>(p->tick_blob_writes.data())[1] = 2;
         }
         else p->n_ctas = (int)t.work.size();
     }
@@ -485,18 +487,21 @@ extern "C" int vep_plan_create(vep_ctx *c, const vep_frame_desc *descs, int n, v
     return VEP_OK;
 }
 
-static int plan_launch(vep_plan *p, void *cuda_stream, bool overlap) {
+static int plan_launch(vep_plan *p, void *cuda_stream, int order) {
     if (!p) return fail(VEP_ERR_INVALID_ARG, "plan is null");
+    if (order < VEP_ORDER_STRICT || order > VEP_ORDER_NONE) return fail(VEP_ERR_INVALID_ARG, "unknown launch order %d", order);
     DeviceGuard g(p->ctx->device);
-    int rc = p->tick_cap ? launch_tick(p->ctx, p->tick_cap, overlap ? p->tick_blob_overlap : p->tick_blob, p->tick_grid, (cudaStream_t)cuda_stream)
+    const std::vector<uint8_t> &blob = order == VEP_ORDER_NONE ? p->tick_blob_overlap : order == VEP_ORDER_WRITES ? p->tick_blob_writes : p->tick_blob;
+    int rc = p->tick_cap ? launch_tick(p->ctx, p->tick_cap, blob, p->tick_grid, (cudaStream_t)cuda_stream)
                          : launch_tables(p->ctx, p->d_frames, p->d_work, p->n_ctas, p->total_items, (cudaStream_t)cuda_stream);
     if (rc) return rc;
     p->ctx->stats.kernel_launches++;
     p->ctx->stats.frames_converted += p->n_converted;
     return VEP_OK;
 }
-extern "C" int vep_plan_launch(vep_plan *p, void *cuda_stream) { return plan_launch(p, cuda_stream, false); }
-extern "C" int vep_plan_launch_overlapped(vep_plan *p, void *cuda_stream) { return plan_launch(p, cuda_stream, true); }
+extern "C" int vep_plan_launch(vep_plan *p, void *cuda_stream) { return plan_launch(p, cuda_stream, VEP_ORDER_STRICT); }
+extern "C" int vep_plan_launch_overlapped(vep_plan *p, void *cuda_stream) { return plan_launch(p, cuda_stream, VEP_ORDER_NONE); }
+extern "C" int vep_plan_launch_ordered(vep_plan *p, void *cuda_stream, int order) { return plan_launch(p, cuda_stream, order); }
 
 extern "C" int vep_plan_info(const vep_plan *p, int *n_converted, int *n_ctas, int64_t *alg_bytes) {
     if (!p) return fail(VEP_ERR_INVALID_ARG, "plan is null");

@@ -546,6 +546,7 @@ template <int NF>
 struct TickParams {
     int32_t n_frames;
     int32_t wait_prior;      // 1: griddepcontrol.wait before touching memory (ordinary stream order);
+                             // 2: wait only before the first global store (the previous kernel did not produce our inputs);
                              // 0: the caller declared this launch independent of the previous kernel
     int32_t uniform_ctas;    // > 0: every frame has this many CTAs and the grid is (uniform_ctas, n_frames):
                              //      blockIdx.y is the frame, no search (homogeneous camera fleets)
@@ -564,7 +565,7 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     // one drains (a 16-frame tick lasts ~27 us, of which ~4 us are ramp and tail); unless the caller
     // vouched for independence, wait here until the previous kernel's writes are complete.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    if (p.wait_prior) asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (p.wait_prior == 1) asm volatile("griddepcontrol.wait;" ::: "memory");
     int cta = blockIdx.x, fi = 0;
     if (p.uniform_ctas > 0) {
         fi = blockIdx.y;
@@ -579,6 +580,7 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     const int first = (cta - p.cta_begin[fi]) * (f.fast == PATH_GENERIC ? kGenericBlocksPerCta : kWarpsPerCta);
 
     if (f.fast == PATH_GENERIC) {
+        if (p.wait_prior == 2) asm volatile("griddepcontrol.wait;" ::: "memory");   // the scalar path stores as it goes
         const int bw = f.w >> 1, nblk = bw * (f.h >> 1);
         for (int q = first + threadIdx.x; q < min(first + kGenericBlocksPerCta, nblk); q += kThreads)
             generic_block(f, q % bw, q / bw);
@@ -698,6 +700,9 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
             }
         }
         __syncwarp();
+        // "ordered writes": loads and arithmetic of the first row pair overlapped the previous kernel's tail; its
+        // writes must be complete before ours land (same output buffer re-used by consecutive launches)
+        if (p.wait_prior == 2 && r == 0) asm volatile("griddepcontrol.wait;" ::: "memory");
         uint8_t *g0 = f.dst + (size_t)(2 * rp) * f.sd + (size_t)seg * kSegBytes;
         uint8_t *g1 = g0 + f.sd;
 #pragma unroll

@@ -99,11 +99,13 @@ class Plan:
         check(self._L.vep_plan_info(self._h, C.byref(n), C.byref(ctas), C.byref(ab)), "vep_plan_info")
         self.n_converted, self.n_ctas, self.alg_bytes = n.value, ctas.value, ab.value
 
-    def launch(self, cuda_stream: int = 0, overlapped: bool = False):
+    def launch(self, cuda_stream: int = 0, overlapped: bool = False, order: Optional[int] = None):
         """overlapped=True: the caller vouches that this launch is independent of the previous kernel
-        launch on the stream (disjoint buffers), so the GPU may overlap the two (see vepb200.h)."""
-        fn = self._L.vep_plan_launch_overlapped if overlapped else self._L.vep_plan_launch
-        check(fn(self._h, C.c_void_p(cuda_stream)), "vep_plan_launch")
+        launch on the stream (disjoint buffers), so the GPU may overlap the two.  `order` selects any of
+        _abi.VEP_ORDER_STRICT / VEP_ORDER_WRITES / VEP_ORDER_NONE explicitly (see vepb200.h)."""
+        if order is None:
+            order = _abi.VEP_ORDER_NONE if overlapped else _abi.VEP_ORDER_STRICT
+        check(self._L.vep_plan_launch_ordered(self._h, C.c_void_p(cuda_stream), int(order)), "vep_plan_launch_ordered")
 
     def close(self):
         if self._h:
