@@ -11,7 +11,9 @@ One JSON line on rank 0:
                the launching stream, K steps back to back, inputs rotate over buffer sets > L2)
   e2e          frames/s through the public API with HOST buffers: FramePath.submit (pinned staging) ->
                tick (H2D, kernel, D2H) -> result_packed, copies inside the timed region
-  roofline     algorithmic bytes (4.5 B/px) per launch / measured launch duration vs MEASURED_PEAKS.json
+  roofline     algorithmic bytes (4.5 B/px) per launch / measured launch duration vs MEASURED_PEAKS.json; the headline
+               launches consecutive ticks with VEP_ORDER_NONE (disjoint buffer sets); the same K ticks with only the
+               stores ordered (`ordered_writes`) and in full stream order (`strict_stream_order`) are reported beside it
   cpu_baseline the reference's CPU path (libswscale sws_scale + tobytes, read_image.py:94-97) timed on
                this box's host cores on a bounded sample of the same frames
 `--impl reference` prints the CPU arm alone in the same shape (rank 0 only under torchrun).
