@@ -417,3 +417,21 @@ def test_known_answer_frames_and_video_legal_levels(path, fmt):
                 assert (got[..., 0] == got[..., 1]).all() and (got[..., 1] == got[..., 2]).all()    # neutral chroma -> gray
         legal = make_planes(fmt, w, h, 3, dist="video")
         assert np.array_equal(gpu_convert(path, fmt, legal), F.to_bgr24(fmt, legal)), (fmt, w, h, "video")
+
+
+def test_8k_frame_and_maximum_dimension(path):
+    planes = make_planes("yuv420p", 7680, 4320, 8)
+    got = gpu_convert(path, "yuv420p", planes)
+    for r0 in range(0, 4320, 1080):      # oracle in bands to bound memory
+        want = F.to_bgr24("yuv420p", (planes[0][r0:r0 + 1080], planes[1][r0 // 2:r0 // 2 + 540], planes[2][r0 // 2:r0 // 2 + 540]))
+        assert np.array_equal(got[r0:r0 + 1080], want), r0
+    # the widest and the tallest frame the ABI admits (16384): thin slices, both paths
+    for fmt, w, h in (("yuv420p", 16384, 2), ("nv12", 16384, 8), ("yuv420p", 2, 16384), ("yuv420p", 16, 16384)):
+        pl = make_planes(fmt, w, h, 9)
+        assert np.array_equal(gpu_convert(path, fmt, pl), F.to_bgr24(fmt, pl)), (fmt, w, h)
+    t = [torch.zeros((2, 16400), dtype=torch.uint8, device="cuda"), torch.zeros((1, 8200), dtype=torch.uint8, device="cuda"),
+         torch.zeros((1, 8200), dtype=torch.uint8, device="cuda")]
+    out = torch.zeros((2, 16400, 3), dtype=torch.uint8, device="cuda")
+    with pytest.raises(VepError) as e:
+        path.convert_batch([desc_from_tensors("yuv420p", t, out)])
+    assert e.value.status == _abi.VEP_ERR_GEOMETRY
