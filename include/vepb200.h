@@ -114,7 +114,8 @@ int vep_plan_launch_overlapped(vep_plan *plan, void *cuda_stream);
 #define VEP_ORDER_WRITES 1
 #define VEP_ORDER_NONE 2
 int vep_plan_launch_ordered(vep_plan *plan, void *cuda_stream, int order);
-/* frames with convert!=0, CTAs per launch, algorithmic bytes (4.5*W*H per converted frame) */
+/* frames with convert!=0, CTAs per launch, algorithmic bytes (read + written: 4.5*W*H per converted 8-bit 4:2:0
+ * frame, 5 for 4:2:2, 6 for 4:4:4 and 10-bit, 4 for gray) */
 int vep_plan_info(const vep_plan *plan, int *n_converted, int *n_ctas, int64_t *alg_bytes);
 void vep_plan_destroy(vep_plan *plan);
 
@@ -141,7 +142,8 @@ int vep_convert_batch_noalloc(const vep_frame_desc *descs, int n, void *cuda_str
 /* ---- host pipeline: camera streams, pinned staging, tick (read_image.py:87-121) --------------
  * stream_open declares a camera (device_id in the reference) with a fixed decoded geometry.
  * `ring_depth` mirrors --memory_buffer / XADD MAXLEN (read_image.py:121): a result stays valid
- * until `ring_depth` newer frames of that stream have been converted (minimum 2 slots are kept). */
+ * until `ring_depth` newer frames of that stream have been converted (ring_depth + VEP_MAX_TICKS_IN_FLIGHT + 2
+ * slots are kept per stream, each with pinned input, pinned output and device buffers). */
 int vep_stream_open(vep_ctx *ctx, int stream_id, int fmt, int width, int height, int ring_depth);
 int vep_stream_close(vep_ctx *ctx, int stream_id);
 
