@@ -469,8 +469,13 @@ def run_gpu(args):
             tot += len(path.result_packed(names[c]))      # the message a producer hands to XADD
         return tot
 
-    for t in range(3):
-        sel, futs = stage_async(t); join(futs); path.tick(); consume(sel)
+    lat = []
+    for t in range(3 + 30):                           # warm-up, then 30 synchronous ticks for the latency figure
+        sel, futs = stage_async(t); join(futs)
+        l0 = time.perf_counter(); path.tick(); consume(sel)
+        if t >= 3 and sel:
+            lat.append((time.perf_counter() - l0) * 1e3)
+    lat.sort()
     barrier()
     torch.cuda.synchronize(dev)
     base_stats = path.stats()
@@ -542,6 +547,8 @@ def run_gpu(args):
                 "steps": e2e_steps, "api": "FramePath.submit from one producer thread per camera (host planes -> pinned staging) + tick_begin/tick_wait (3 ticks in flight) + result_packed",
                 "pcie_gbs": round((h2d_per_step + d2h_per_step) * e2e_steps / e2e_s / 1e9, 2), "message_bytes": msg_bytes,
                 "producer_threads": pool._max_workers,
+                "sync_tick_latency_ms": {"p50": round(lat[len(lat) // 2], 3), "max": round(lat[-1], 3),
+                                         "what": "one tick alone, staged planes -> packed messages readable (H2D + kernel + D2H, no overlap)"} if lat else None,
                 "decoder_writes_into_pinned_slot": {"value": round(zc_value, 1), "unit": UNIT,
                                                     "api": "vep_acquire_input/vep_commit_input instead of vep_submit: no host staging copy before the H2D"}},
         "gpu_launches": gpu_launches,
