@@ -53,7 +53,13 @@ typedef enum {
 /* One frame of a batched conversion, all pointers in DEVICE memory.
  * Takes the place of one `frame.to_ndarray(format='bgr24')` call (read_image.py:94):
  * plane[]/stride[] are the AVFrame planes and linesizes, dst is the (H, W, 3) uint8 result
- * (dst_stride = 3*width for the contiguous array PyAV returns after its padding strip). */
+ * (dst_stride = 3*width for the contiguous array PyAV returns after its padding strip).
+ * Any even geometry and any alignment is accepted and gives the same bytes.  The fast (vector) path needs
+ * 16-byte aligned plane and dst pointers and strides that are multiples of 16 (planar 8-bit chroma: 8); for
+ * 8-bit formats the width itself may be any even number.  With such strides and a width that is not a multiple
+ * of 16 the kernel READS up to 15 bytes of padding behind the visible samples of a row (as libswscale does with
+ * an AVFrame's padded linesize) — every row, the last one included, must therefore have `stride` readable bytes;
+ * nothing outside the visible 3*width bytes of an output row is ever written. */
 typedef struct {
     const uint8_t *plane[3]; /* Y,U,V  (nv12/nv21: Y,UV,NULL) */
     int32_t stride[3];       /* bytes per row of each plane */
@@ -96,6 +102,8 @@ void vep_destroy(vep_ctx *ctx);
  * vep_convert_batch validates, uploads the table and launches; a plan does the first two once
  * so a fixed camera set costs one launch per tick. */
 int vep_convert_batch(vep_ctx *ctx, const vep_frame_desc *descs, int n, void *cuda_stream);
+/* The same with an explicit launch order (VEP_ORDER_*, below); vep_convert_batch is VEP_ORDER_STRICT. */
+int vep_convert_batch_ordered(vep_ctx *ctx, const vep_frame_desc *descs, int n, void *cuda_stream, int order);
 int vep_plan_create(vep_ctx *ctx, const vep_frame_desc *descs, int n, vep_plan **out);
 int vep_plan_launch(vep_plan *plan, void *cuda_stream);
 /* Same launch, but the caller asserts that it neither reads nor overwrites anything the PREVIOUS
@@ -114,6 +122,9 @@ int vep_plan_launch_overlapped(vep_plan *plan, void *cuda_stream);
 #define VEP_ORDER_WRITES 1
 #define VEP_ORDER_NONE 2
 int vep_plan_launch_ordered(vep_plan *plan, void *cuda_stream, int order);
+/* plans[0..n) launched back to back on one stream with one call (all of one device): what a native producer
+ * converting tick after tick does; saves the per-call overhead of n separate vep_plan_launch_ordered calls. */
+int vep_plan_launch_sequence(vep_plan *const *plans, int n, void *cuda_stream, int order);
 /* frames with convert!=0, CTAs per launch, algorithmic bytes (read + written: 4.5*W*H per converted 8-bit 4:2:0
  * frame, 5 for 4:2:2, 6 for 4:4:4 and 10-bit, 4 for gray) */
 int vep_plan_info(const vep_plan *plan, int *n_converted, int *n_ctas, int64_t *alg_bytes);
@@ -126,15 +137,19 @@ void vep_plan_destroy(vep_plan *plan);
  * real-time loop that cannot take cudaMalloc's device-wide synchronisation mid-stream.  Needs no
  * vep_ctx; works on the CURRENT device and on the caller's stream; calls no cudaMalloc/cudaFree or
  * any other allocating routine.  Its descriptor tables live in a fixed array inside the library's
- * CUDA module (about 532 KB on every GPU that loads the library, until the process exits), hence the
+ * CUDA module (545,024 bytes on every GPU that loads the library, until the process exits), hence the
  * limits: at most VEP_NOALLOC_MAX_FRAMES converted frames and VEP_NOALLOC_MAX_CTAS thread blocks per
- * call (one block covers 8 x 512 px x 2 rows: a 1080p frame takes 270, 4K takes 1080); larger batches
- * are refused with VEP_ERR_INVALID_ARG and the text says which limit — split them.
+ * call.  On the vector path (8-bit 4:2:0 planar / NV12 / NV21 with aligned planes) one block covers
+ * 8 x 512 px x 2 rows: a 1080p frame takes 270 blocks, 4K takes 1080; every other frame (4:2:2, 4:4:4,
+ * gray, 10-bit, unaligned planes) runs the scalar path at 1024 2x2 blocks per thread block: 507 for
+ * 1080p.  Larger batches are refused with VEP_ERR_INVALID_ARG and the text says which limit — split them.
  * The first call on each device also resolves the array's address on that device; make that first
  * call before any stream capture is begun.  All calls share the one array per device and each call
  * rewrites it: calls whose GPU work can overlap (different streams, different threads) race and
- * must be serialised by the caller; calls queued on one stream are safe.  Outputs are byte-identical
- * to vep_convert_batch. */
+ * must be serialised by the caller; calls queued on one stream are safe.  The tables are uploaded from
+ * ordinary (pageable) host memory inside the library, so a call may hold the calling thread until work
+ * queued earlier on the same stream has drained — keep that in mind in a loop with a deadline.  Outputs
+ * are byte-identical to vep_convert_batch. */
 #define VEP_NOALLOC_MAX_FRAMES 256
 #define VEP_NOALLOC_MAX_CTAS 65536
 int vep_convert_batch_noalloc(const vep_frame_desc *descs, int n, void *cuda_stream);
@@ -145,7 +160,13 @@ int vep_convert_batch_noalloc(const vep_frame_desc *descs, int n, void *cuda_str
  * until `ring_depth` newer frames of that stream have been converted (ring_depth + VEP_MAX_TICKS_IN_FLIGHT + 2
  * slots are kept per stream, each with pinned input, pinned output and device buffers). */
 int vep_stream_open(vep_ctx *ctx, int stream_id, int fmt, int width, int height, int ring_depth);
+/* Not while ticks are in flight (VEP_ERR_BUSY) and not while another thread is inside a call for this stream. */
 int vep_stream_close(vep_ctx *ctx, int stream_id);
+/* Helper threads for vep_submit's staging copy (default 0).  One core copies 10-16 GB/s into pinned memory, a
+ * PCIe Gen5 link takes 55: frames of 4 MB and more (4K) are then cut into row bands copied by the submitting
+ * thread and n helpers.  Smaller frames are always copied by the submitting thread alone (one producer thread per
+ * camera already covers them, as the reference's one process per camera does). */
+int vep_set_staging_threads(vep_ctx *ctx, int n);
 
 /* Hand one decoded frame (HOST pointers: AVFrame planes + linesizes) to the library.  The planes
  * are copied into pinned staging before the call returns, so the caller's frame may be freed.
@@ -154,7 +175,8 @@ int vep_stream_close(vep_ctx *ctx, int stream_id);
 int vep_submit(vep_ctx *ctx, int stream_id, const uint8_t *const plane[3], const int32_t stride[3],
                const vep_frame_meta *meta, int convert);
 /* Zero-copy variant: get pointers into the next pinned staging slot (a decoder can write its
- * planes there directly), then commit it. */
+ * planes there directly), then commit it.  stride_out is the row pitch of each plane in the slot: the row bytes
+ * when they are a multiple of 16, else rounded up to 64. */
 int vep_acquire_input(vep_ctx *ctx, int stream_id, uint8_t *plane_out[3], int32_t stride_out[3]);
 int vep_commit_input(vep_ctx *ctx, int stream_id, const vep_frame_meta *meta);
 
@@ -163,8 +185,13 @@ int vep_commit_input(vep_ctx *ctx, int stream_id, const vep_frame_meta *meta);
  * begin+wait.  Up to VEP_MAX_TICKS_IN_FLIGHT ticks may be in flight (begin, begin, wait, …) so the
  * staging copy and H2D of later ticks overlap the D2H of earlier ones (PCIe is full duplex). */
 int vep_tick_begin(vep_ctx *ctx, int *n_frames);
-int vep_tick_wait(vep_ctx *ctx);
-int vep_tick(vep_ctx *ctx, int *n_frames);
+int vep_tick_wait(vep_ctx *ctx);   /* waits for the OLDEST tick in flight */
+int vep_tick(vep_ctx *ctx, int *n_frames);   /* begin + wait for THAT tick (and any older one) */
+/* Ticketed form for several ticking threads or sparse ticks: begin hands out a ticket (ticks that found nothing
+ * to convert return the ticket of the newest real tick, 0 if there never was one); wait_ticket returns once that
+ * tick and all older ones have landed, whoever else has begun or waited for ticks meanwhile. */
+int vep_tick_begin_ticket(vep_ctx *ctx, int *n_frames, uint64_t *ticket);
+int vep_tick_wait_ticket(vep_ctx *ctx, uint64_t ticket);
 
 /* Newest converted frame of a stream: pointer to H*W*3 contiguous BGR bytes in pinned host
  * memory (what `np.ndarray.tobytes(img)` yields at read_image.py:97) and shape = {H, W, 3}
@@ -180,7 +207,11 @@ int vep_result_packed(vep_ctx *ctx, int stream_id, const uint8_t **msg, size_t *
  * until the stream is fed again. */
 int vep_result_packed_at(vep_ctx *ctx, int stream_id, int age, const uint8_t **msg, size_t *len);
 int vep_result_at(vep_ctx *ctx, int stream_id, int age, const uint8_t **bgr, size_t *len, int32_t shape[3]);
-/* Device-side view of the same result for GPU consumers (zero-copy; valid like vep_result). */
+/* Device-side view of the same result for GPU consumers (zero-copy; valid like vep_result).  On the device a row
+ * occupies *row_pitch bytes: 3*width when that is a multiple of 16 (every common resolution), else 3*width rounded
+ * up to 64 (the copy to the host removes the padding).  vep_result_device serves the unpadded case only and returns
+ * VEP_ERR_GEOMETRY otherwise. */
+int vep_result_device_pitched(vep_ctx *ctx, int stream_id, const uint8_t **bgr_dev, int32_t shape[3], int32_t *row_pitch);
 int vep_result_device(vep_ctx *ctx, int stream_id, const uint8_t **bgr_dev, int32_t shape[3]);
 
 /* ---- VideoFrame wire framing alone (read_image.py:99-119 minus the payload copy) -------------

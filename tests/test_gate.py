@@ -21,6 +21,7 @@ def _product_walk(events):
                 if o.first_frame_only:
                     break
                 g.frame_published(kfo, q)
+            g.packet_done()
     return out
 
 

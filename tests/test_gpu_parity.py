@@ -11,7 +11,7 @@ torch = pytest.importorskip("torch")
 
 from oracle import formulas as F  # noqa: E402
 from oracle import swscale_live as L  # noqa: E402
-from video_edge_ai_proxy_b200 import FramePath, VepError, desc_from_device_ptrs, desc_from_tensors  # noqa: E402
+from video_edge_ai_proxy_b200 import FramePath, VepError, desc_from_device_ptrs, desc_from_tensors, launch_sequence  # noqa: E402
 from video_edge_ai_proxy_b200 import _abi  # noqa: E402
 from video_edge_ai_proxy_b200.synth import exhaustive_yuv_frame, make_planes  # noqa: E402
 
@@ -181,85 +181,92 @@ def test_linearity_free_properties_at_full_size(path):
     plan.close()
 
 
-def test_persistent_tma_kernel_bit_identical(golden_pixels, small_frames):
-    """The alternative kernel (VEP_KERNEL=persistent: per-warp TMA bulk-copy pipelines) on every path."""
-    old = os.environ.get("VEP_KERNEL")
-    os.environ["VEP_KERNEL"] = "persistent"
-    try:
-        with FramePath(0) as p:
-            for r in golden_pixels["rows"]:
-                if r["path"] == "simd":
-                    out = gpu_convert(p, r["fmt"], make_planes(r["fmt"], r["w"], r["h"], r["seed"]))
-                    assert _digest(out) == (r["sum"], r["sha256"]), r
-            for fmt, w, h, seed, planes, want in small_frames:
-                assert np.array_equal(gpu_convert(p, fmt, planes), want), (fmt, w, h)
-            for fmt, w, h in (("yuv420p", 16, 8), ("yuv420p", 48, 8), ("nv12", 528, 16), ("yuvj420p", 1040, 8), ("nv12", 32, 8),
-                              ("yuv420p", 64, 8), ("yuv420p", 496, 4), ("nv12", 18, 10), ("nv21", 1280, 720), ("nv21", 48, 8),
-                              ("yuvj422p", 640, 480), ("yuv422p", 50, 6), ("yuv420p10le", 640, 480), ("yuv420p10le", 50, 10)):
-                planes = make_planes(fmt, w, h, w + h)
-                assert np.array_equal(gpu_convert(p, fmt, planes), F.to_bgr24(fmt, planes)), (fmt, w, h)
-            # a mixed batch in one launch: bulk, vector and generic frames together
-            specs = [("yuv420p", 1920, 1080, 1), ("nv12", 1280, 720, 2), ("yuv420p", 48, 8, 3), ("yuvj420p", 642, 482, 4), ("nv12", 3840, 2160, 5)]
-            descs, keep = [], []
-            for fmt, w, h, seed in specs:
-                planes = make_planes(fmt, w, h, seed)
-                t = [torch.from_numpy(q).cuda() for q in planes]
-                out = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
-                descs.append(desc_from_tensors(fmt, t, out))
-                keep.append((fmt, planes, t, out))
-            p.convert_batch(descs, torch.cuda.current_stream().cuda_stream)
-            torch.cuda.synchronize()
-            for fmt, planes, t, out in keep:
-                assert np.array_equal(out.cpu().numpy(), F.to_bgr24(fmt, planes)), fmt
-    finally:
-        if old is None:
-            os.environ.pop("VEP_KERNEL", None)
-        else:
-            os.environ["VEP_KERNEL"] = old
+def _padded_case(fmt, w, h, seed, extra=0, off=0, fill_in=0x33, fill_out=0x5A):
+    """Planes and output in buffers whose rows are padded to multiples of 16 bytes (+ extra) and start 16-byte
+    aligned (+ off): the layout of an AVFrame with padded linesize, and what the host pipeline stages."""
+    planes = make_planes(fmt, w, h, seed)
+    bufs, ptrs, strides = [], [], []
+    for p in planes:
+        pb = np.ascontiguousarray(p).view(np.uint8).reshape(p.shape[0], -1)     # rows as bytes
+        ph, pw = pb.shape
+        st = (pw + 15) // 16 * 16 + extra
+        buf = torch.full((ph * st + off + 64,), fill_in, dtype=torch.uint8, device="cuda")
+        view = buf[off:off + ph * st].view(ph, st)
+        view[:, :pw] = torch.from_numpy(pb).cuda()
+        bufs.append(buf); ptrs.append(view.data_ptr()); strides.append(st)
+    dstride = (3 * w + 15) // 16 * 16 + extra
+    obuf = torch.full((h * dstride + off + 64,), fill_out, dtype=torch.uint8, device="cuda")
+    desc = desc_from_device_ptrs(fmt, w, h, ptrs, strides, obuf.data_ptr() + off, dstride)
+    return desc, (fmt, w, h, off, dstride, planes, bufs, obuf)
 
 
-def _with_env(env):
-    class _Ctx:
-        def __enter__(self_):
-            self_.old = {k: os.environ.get(k) for k in env}
-            os.environ.update(env)
-
-        def __exit__(self_, *a):
-            for k, v in self_.old.items():
-                if v is None:
-                    os.environ.pop(k, None)
-                else:
-                    os.environ[k] = v
-    return _Ctx()
+def _check_padded(case, fill_out=0x5A):
+    fmt, w, h, off, dstride, planes, bufs, obuf = case
+    o = obuf.cpu().numpy()
+    rows = o[off:off + h * dstride].reshape(h, dstride)
+    assert np.array_equal(rows[:, :3 * w].reshape(h, w, 3), F.to_bgr24(fmt, planes)), (fmt, w, h, off, dstride)
+    # nothing outside the visible W*3 bytes of each row is written (swscale overwrites padding; we must not)
+    assert (rows[:, 3 * w:] == fill_out).all() and (o[:off] == fill_out).all() and (o[off + h * dstride:] == fill_out).all(), (fmt, w, h, off, dstride)
 
 
-@pytest.mark.parametrize("env", [{"VEP_RPT": "1", "VEP_MINB": "5"}, {"VEP_RPT": "1", "VEP_MINB": "6"}, {"VEP_RPT": "1", "VEP_MINB": "8"},
-                                 {"VEP_RPT": "2", "VEP_MINB": "3"}, {"VEP_RPT": "2", "VEP_MINB": "4"}, {"VEP_KERNEL": "oneshot"}])
-def test_tick_kernel_variants_bit_identical(env, small_frames):
-    with _with_env(env), FramePath(0) as p:
-        for fmt, w, h, seed, planes, want in small_frames:
-            assert np.array_equal(gpu_convert(p, fmt, planes), want), (env, fmt, w, h)
-        for fmt, w, h in (("yuv420p", 1920, 1080), ("nv12", 1920, 1080), ("yuvj420p", 640, 480), ("yuv420p", 528, 6), ("nv12", 1040, 10),
-                          ("yuv420p", 16, 2), ("nv12", 3840, 2160), ("yuv420p", 642, 482), ("nv12", 64, 14),
-                          ("nv21", 1280, 720), ("yuvj422p", 1280, 720), ("yuv422p", 528, 6), ("nv21", 38, 12), ("yuvj422p", 50, 6),
-                          ("yuv420p10le", 1280, 720), ("yuv420p10le", 528, 10), ("yuv420p10le", 38, 12)):
-            planes = make_planes(fmt, w, h, w + h)
-            assert np.array_equal(gpu_convert(p, fmt, planes), F.to_bgr24(fmt, planes)), (env, fmt, w, h)
-        # 40 frames in one launch (128-entry parameter table) and 150 frames (falls back to the device table)
-        for n in (40, 150):
-            descs, keep = [], []
-            for i in range(n):
-                fmt, w, h = (("yuv420p", 320, 240), ("nv12", 352, 288), ("yuvj420p", 160, 120), ("yuv420p", 50, 6),
-                             ("yuvj422p", 320, 240), ("nv21", 64, 48), ("yuv420p10le", 160, 120), ("yuvj444p", 96, 64), ("gray", 64, 32))[i % 9]
-                planes = make_planes(fmt, w, h, i)
-                t = [torch.from_numpy(q).cuda() for q in planes]
-                out = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
-                descs.append(desc_from_tensors(fmt, t, out))
-                keep.append((fmt, planes, t, out))
-            p.convert_batch(descs, torch.cuda.current_stream().cuda_stream)
-            torch.cuda.synchronize()
-            for fmt, planes, t, out in keep:
-                assert np.array_equal(out.cpu().numpy(), F.to_bgr24(fmt, planes)), (env, n, fmt)
+@pytest.mark.parametrize("fmt", ALL_FORMATS)
+def test_ragged_widths_on_the_vector_path(path, fmt):
+    """Widths that are not a multiple of 16 with 16-byte padded rows (what the host pipeline stages and what a
+    decoder's AVFrame looks like): the vector path with a partial last lane.  Visible bytes equal the oracle, the
+    row padding of the output keeps its sentinel, whatever garbage the input padding holds."""
+    for w in (2, 6, 18, 34, 50, 130, 510, 514, 854, 1366, 1922):
+        for h, extra, off in ((8, 0, 0), (10, 16, 0), (18, 32, 16)):
+            for fill_in in (0x00, 0xFF):                 # the input padding is read: it must not matter what it holds
+                d, case = _padded_case(fmt, w, h, 7 * w + h, extra, off, fill_in=fill_in)
+                path.convert_batch([d], torch.cuda.current_stream().cuda_stream)
+                torch.cuda.synchronize()
+                _check_padded(case)
+
+
+def test_ragged_widths_mixed_launch_and_device_table(path):
+    """The same layouts in one mixed launch (parameter table) and in a 140-frame launch (device table)."""
+    fmts_w = [("yuv420p", 854, 480), ("nv12", 1366, 768), ("yuvj420p", 50, 6), ("yuv422p", 854, 16), ("gray", 1366, 10),
+              ("yuv444p", 130, 8), ("nv21", 514, 12), ("yuv420p", 1920, 1080), ("yuv420p10le", 50, 10), ("yuvj422p", 18, 4)]
+    for n in (len(fmts_w), 140):
+        descs, cases = [], []
+        for i in range(n):
+            fmt, w, h = fmts_w[i % len(fmts_w)]
+            if n > 100:
+                h = min(h, 24)
+            d, case = _padded_case(fmt, w, h, 100 + i, extra=16 * (i % 2))
+            descs.append(d); cases.append(case)
+        path.convert_batch(descs, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        for case in cases:
+            _check_padded(case)
+
+
+def test_large_batches_parameter_table_and_device_table(path, small_frames):
+    for fmt, w, h, seed, planes, want in small_frames:
+        assert np.array_equal(gpu_convert(path, fmt, planes), want), (fmt, w, h)
+    # 40 frames in one launch (128-entry parameter table) and 150 frames (falls back to the device table)
+    for n in (40, 150):
+        descs, keep = [], []
+        for i in range(n):
+            fmt, w, h = (("yuv420p", 320, 240), ("nv12", 352, 288), ("yuvj420p", 160, 120), ("yuv420p", 50, 6),
+                         ("yuvj422p", 320, 240), ("nv21", 64, 48), ("yuv420p10le", 160, 120), ("yuvj444p", 96, 64), ("gray", 64, 32))[i % 9]
+            planes = make_planes(fmt, w, h, i)
+            t = [torch.from_numpy(q).cuda() for q in planes]
+            out = torch.empty((h, w, 3), dtype=torch.uint8, device="cuda")
+            descs.append(desc_from_tensors(fmt, t, out))
+            keep.append((fmt, planes, t, out))
+        path.convert_batch(descs, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        for fmt, planes, t, out in keep:
+            assert np.array_equal(out.cpu().numpy(), F.to_bgr24(fmt, planes)), (n, fmt)
+        plan = path.plan(descs)                          # the same batch as a plan, launched twice in one native call
+        for _, _, _, out in keep:
+            out.zero_()
+        launch_sequence([plan, plan], torch.cuda.current_stream().cuda_stream, _abi.VEP_ORDER_STRICT)
+        torch.cuda.synchronize()
+        for fmt, planes, t, out in keep:
+            assert np.array_equal(out.cpu().numpy(), F.to_bgr24(fmt, planes)), (n, fmt, "plan")
+        plan.close()
 
 
 def test_overlapped_and_ordered_launches(path):
@@ -298,33 +305,26 @@ def test_overlapped_and_ordered_launches(path):
                 pln.launch(st, order=order)
         torch.cuda.synchronize()
         assert np.array_equal(shared.cpu().numpy(), F.to_bgr24("yuv420p", keep[-1][0])), order
+    # the same through one native call per round (vep_plan_launch_sequence) and through vep_convert_batch_ordered
+    shared.zero_()
+    for _ in range(3):
+        launch_sequence(plans, st, _abi.VEP_ORDER_WRITES)
+    torch.cuda.synchronize()
+    assert np.array_equal(shared.cpu().numpy(), F.to_bgr24("yuv420p", keep[-1][0]))
+    shared.zero_()
+    for pl, t in keep:
+        path.convert_batch([desc_from_tensors("yuv420p", t, shared)], st, order=_abi.VEP_ORDER_WRITES)
+    torch.cuda.synchronize()
+    assert np.array_equal(shared.cpu().numpy(), F.to_bgr24("yuv420p", keep[-1][0]))
+    launch_sequence([], st)
     with pytest.raises(VepError):
         plans[0].launch(st, order=7)
+    with pytest.raises(VepError):
+        launch_sequence(plans, st, 7)
     for _, _, pln in sets:
         pln.close()
     for pln in plans:
         pln.close()
-
-
-def test_all_store_modes_bit_identical():
-    planes = make_planes("yuv420p", 1920, 1080, 42)
-    want = F.to_bgr24("yuv420p", planes)
-    nv = make_planes("nv12", 1040, 64, 43)
-    want_nv = F.to_bgr24("nv12", nv)
-    old = os.environ.get("VEP_STORE_MODE")
-    try:
-        for mode in ("0", "1", "2"):
-            os.environ["VEP_STORE_MODE"] = mode
-            os.environ["VEP_KERNEL"] = "oneshot"
-            with FramePath(0) as p:
-                assert np.array_equal(gpu_convert(p, "yuv420p", planes), want), mode
-                assert np.array_equal(gpu_convert(p, "nv12", nv), want_nv), mode
-    finally:
-        os.environ.pop("VEP_KERNEL", None)
-        if old is None:
-            os.environ.pop("VEP_STORE_MODE", None)
-        else:
-            os.environ["VEP_STORE_MODE"] = old
 
 
 def test_rejections(path):
@@ -367,6 +367,9 @@ def test_random_geometry_fuzz_one_launch_per_round(path):
                 h = max(h, 8)
             pad = int(rng.choice([0, 0, 16, 32, 7, 48]))
             off = int(rng.choice([0, 0, 16, 8, 3]))
+            align_rows = bool(rng.integers(2))            # half the frames: rows padded up to 16-byte multiples (vector path for any width)
+            if align_rows:
+                pad, off = pad & ~15, off & ~15
             if fmt == "yuv420p10le":                      # 16-bit samples: planes and strides stay 2-byte aligned
                 pad, off = pad & ~1, off & ~1
             planes = make_planes(fmt, w, h, 1000 * rnd + i)
@@ -374,11 +377,12 @@ def test_random_geometry_fuzz_one_launch_per_round(path):
             for p in planes:
                 p = np.ascontiguousarray(p).view(np.uint8).reshape(p.shape[0], -1)     # rows as bytes
                 ph, pw = p.shape
-                buf = torch.full((ph * (pw + pad) + off + 64,), 0x33, dtype=torch.uint8, device="cuda")
-                view = buf[off:off + ph * (pw + pad)].view(ph, pw + pad)
+                st_ = ((pw + 15) // 16 * 16 if align_rows else pw) + pad
+                buf = torch.full((ph * st_ + off + 64,), 0x33, dtype=torch.uint8, device="cuda")
+                view = buf[off:off + ph * st_].view(ph, st_)
                 view[:, :pw] = torch.from_numpy(p).cuda()
-                bufs.append(buf); ptrs.append(view.data_ptr()); strides.append(pw + pad)
-            dstride = 3 * w + pad
+                bufs.append(buf); ptrs.append(view.data_ptr()); strides.append(st_)
+            dstride = ((3 * w + 15) // 16 * 16 if align_rows else 3 * w) + pad
             obuf = torch.full((h * dstride + off + 64,), 0x5A, dtype=torch.uint8, device="cuda")
             descs.append(desc_from_device_ptrs(fmt, w, h, ptrs, strides, obuf.data_ptr() + off, dstride))
             keep.append((fmt, w, h, pad, off, dstride, planes, bufs, obuf))

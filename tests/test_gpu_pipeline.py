@@ -421,3 +421,109 @@ def test_read_image_drop_in_thread():
         img = np.frombuffer(vf.data, np.uint8).reshape([d.size for d in vf.shape.dim])
         assert np.array_equal(img, F.to_bgr24(fmt, make_planes(fmt, w, h, 500 + idx)))
     # a bad frame is dropped with the reference's message and the thread survives (read_image.py:130-131)
+
+
+def test_ragged_widths_through_the_pipeline(path):
+    """854 x 480, 1366 x 768 and friends: the staged planes and the device output get padded rows (vector path),
+    the copy back to the host removes the padding — results are the tight (H, W, 3) arrays and messages."""
+    cams = [("a", "yuv420p", 854, 480), ("b", "nv12", 1366, 768), ("c", "yuvj422p", 854, 480), ("d", "gray", 1366, 10),
+            ("e", "yuv444p", 130, 8), ("f", "yuv420p10le", 854, 480), ("g", "yuv420p", 1928, 1080), ("h", "nv21", 50, 10)]
+    for i, (name, fmt, w, h) in enumerate(cams):
+        path.open_stream(name, fmt, w, h)
+        path.submit(name, make_planes(fmt, w, h, 40 + i), make_meta(timestamp=i + 1, frame_type="I"))
+    assert path.tick() == len(cams)
+    for i, (name, fmt, w, h) in enumerate(cams):
+        want = F.to_bgr24(fmt, make_planes(fmt, w, h, 40 + i))
+        got = path.result(name)
+        assert got.shape == (h, w, 3) and got.flags["C_CONTIGUOUS"] and np.array_equal(got, want), name
+        msg = bytes(path.result_packed(name))
+        assert want.tobytes() in msg and len(msg) < h * w * 3 + 256
+        t = path.result_tensor(name)                      # strided view when the device rows are padded
+        assert tuple(t.shape) == (h, w, 3) and np.array_equal(t.cpu().numpy(), want), name
+    # zero-copy staging hands out the padded pitch
+    planes = make_planes("yuv420p", 854, 480, 99)
+    views = path.acquire_input("a")
+    for v, p in zip(views, planes):
+        assert v.shape == p.shape
+        v[...] = p
+    path.commit_input("a")
+    path.tick()
+    assert np.array_equal(path.result("a"), F.to_bgr24("yuv420p", planes))
+    # the unpitched device accessor refuses padded rows instead of handing out a wrong shape
+    import ctypes as C
+    p, shp = C.c_void_p(), (C.c_int32 * 3)()
+    assert _abi.lib().vep_result_device(path._ctx, path._sid("a"), C.byref(p), shp) == _abi.VEP_ERR_GEOMETRY
+    assert _abi.lib().vep_result_device(path._ctx, path._sid("g"), C.byref(p), shp) == _abi.VEP_ERR_GEOMETRY   # 1928*3 % 16 != 0
+
+
+def test_tick_waits_for_the_tick_it_began_with_two_tickers(path):
+    """Two threads share one FramePath and each runs submit -> tick -> result for its own camera (what two
+    ReadImage threads of one process do).  Every result must be the frame that very thread just submitted."""
+    w, h, rounds = 640, 480, 40
+    names = ("left", "right")
+    frames = {n: [make_planes("yuv420p", w, h, 1000 * k + i) for i in range(4)] for k, n in enumerate(names)}
+    want = {n: [F.to_bgr24("yuv420p", p) for p in frames[n]] for n in names}
+    for n in names:
+        path.open_stream(n, "yuv420p", w, h)
+    errors = []
+    start = threading.Barrier(2)
+
+    def worker(name):
+        try:
+            start.wait()
+            for r in range(rounds):
+                path.submit(name, frames[name][r % 4], make_meta(timestamp=r + 1))
+                path.tick()
+                if not np.array_equal(path.result(name), want[name][r % 4]):
+                    errors.append((name, r))
+        except Exception as e:      # pragma: no cover
+            errors.append((name, repr(e)))
+
+    ts = [threading.Thread(target=worker, args=(n,)) for n in names]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errors, errors[:5]
+
+
+def test_tickets_and_empty_ticks(path):
+    w, h = 320, 240
+    path.open_stream("cam", "yuv420p", w, h, memory_buffer=2)
+    n, t0 = path.tick_begin_ticket()
+    assert (n, t0) == (0, 0)                              # nothing staged, no tick ever: ticket 0, waiting is a no-op
+    path.tick_wait_ticket(t0)
+    planes = [make_planes("yuv420p", w, h, s) for s in range(3)]
+    path.submit("cam", planes[0])
+    n1, t1 = path.tick_begin_ticket()
+    path.submit("cam", planes[1])
+    n2, t2 = path.tick_begin_ticket()
+    n3, t3 = path.tick_begin_ticket()                     # empty: carries the newest real ticket
+    assert (n1, n2, n3) == (1, 1, 0) and t2 == t1 + 1 and t3 == t2
+    path.tick_wait_ticket(t3)                             # both real ticks have landed
+    assert np.array_equal(path.result("cam"), F.to_bgr24("yuv420p", planes[1]))
+    assert np.array_equal(path.result("cam", age=1), F.to_bgr24("yuv420p", planes[0]))
+    path.tick_wait_ticket(t1)                             # already retired: returns at once
+    path.tick_wait()                                      # nothing in flight: fine
+
+
+def test_staging_helper_threads_split_a_4k_frame(path):
+    w, h = 3840, 2160
+    path.set_staging_threads(3)
+    for fmt in ("nv12", "yuv420p"):
+        planes = make_planes(fmt, w, h, 21)
+        # decoder-style padded linesize on the source side as well
+        padded = [np.full((p.shape[0], p.shape[1] + 64), 0xEE, np.uint8) for p in planes]
+        for b, p in zip(padded, planes):
+            b[:, :p.shape[1]] = p
+        path.open_stream(fmt, fmt, w, h)
+        path.submit(fmt, [b[:, :p.shape[1]] for b, p in zip(padded, planes)])
+        assert path.tick() == 1
+        assert np.array_equal(path.result(fmt), F.to_bgr24(fmt, planes)), fmt
+    path.set_staging_threads(0)
+    planes = make_planes("nv12", w, h, 22)
+    path.submit("nv12", planes)
+    path.tick()
+    assert np.array_equal(path.result("nv12"), F.to_bgr24("nv12", planes))
+    with pytest.raises(VepError):
+        path.set_staging_threads(1000)

@@ -5,7 +5,8 @@ a host application that owns the allocator, a real-time loop — so its descript
 fixed array inside the library instead of cudaMalloc'ed buffers.  The check: on the same inputs its
 output must equal, byte for byte (the bar every test here uses), what the ordinary entry point
 vep_convert_batch writes — on two calls in a row, because the second call re-uses the array that
-still holds the first call's tables (a larger batch first, then a smaller, different one).
+still holds the first call's tables (a larger batch first, then a smaller, different one) — and, so
+that the comparison is not only kernel against kernel, what the CPU oracle computes for those planes.
 
 Collected last on purpose (file name), so a run that stops at the first failure has already run
 everything else.  Needs no state from other tests and leaves none behind.
@@ -19,6 +20,7 @@ pytestmark = pytest.mark.gpu
 
 torch = pytest.importorskip("torch")
 
+from oracle import formulas  # noqa: E402
 from video_edge_ai_proxy_b200 import FramePath, VepError, _abi, desc_from_tensors  # noqa: E402
 from video_edge_ai_proxy_b200.synth import make_planes  # noqa: E402
 
@@ -58,6 +60,8 @@ def test_noalloc_entry_point_matches_convert_batch_twice_in_a_row():
                 ref, new = a.cpu().numpy(), b.cpu().numpy()
                 assert ref.any(), "reference output was not written"
                 assert np.array_equal(new, ref), (fmt, w, h)   # bit-exact, as everywhere in this suite
+            for (fmt, w, h, seed), (_, b) in zip(specs, k_new):    # and against the oracle itself
+                assert np.array_equal(b.cpu().numpy(), formulas.to_bgr24(fmt, make_planes(fmt, w, h, seed))), (fmt, w, h, "oracle")
 
 
 def test_noalloc_limits_and_skips():

@@ -11,11 +11,12 @@ libvepb200.so, hand-written sm_100a CUDA behind the C ABI of include/vepb200.h):
 """
 from ._abi import VepError, build_library  # noqa: F401
 from .frame_path import (FramePath, Plan, convert_batch_noalloc, desc_from_device_ptrs, desc_from_tensors,  # noqa: F401
-                         make_meta, to_ndarray_bgr24, videoframe_framing)
+                         launch_sequence, make_meta, to_ndarray_bgr24, videoframe_framing)
 from .gate import CameraControl, DecodeGate, camera_active, poll_control  # noqa: F401
 from .producer import FrameProducer  # noqa: F401
 from .shard import assign_cameras  # noqa: F401
 
 __all__ = ["FramePath", "Plan", "make_meta", "videoframe_framing", "to_ndarray_bgr24", "DecodeGate",
            "CameraControl", "camera_active", "poll_control", "FrameProducer", "assign_cameras",
-           "VepError", "build_library", "desc_from_device_ptrs", "desc_from_tensors", "convert_batch_noalloc"]
+           "VepError", "build_library", "desc_from_device_ptrs", "desc_from_tensors", "convert_batch_noalloc",
+           "launch_sequence"]

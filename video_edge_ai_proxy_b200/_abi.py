@@ -53,15 +53,18 @@ SIGNATURES = {
     "vep_create": (_i, [_i, _pp]),
     "vep_destroy": (None, [_p]),
     "vep_convert_batch": (_i, [_p, C.POINTER(FrameDesc), _i, _p]),
+    "vep_convert_batch_ordered": (_i, [_p, C.POINTER(FrameDesc), _i, _p, _i]),
     "vep_convert_batch_noalloc": (_i, [C.POINTER(FrameDesc), _i, _p]),
     "vep_plan_create": (_i, [_p, C.POINTER(FrameDesc), _i, _pp]),
     "vep_plan_launch": (_i, [_p, _p]),
     "vep_plan_launch_overlapped": (_i, [_p, _p]),
     "vep_plan_launch_ordered": (_i, [_p, _p, _i]),
+    "vep_plan_launch_sequence": (_i, [C.POINTER(C.c_void_p), _i, _p, _i]),
     "vep_plan_info": (_i, [_p, _ip, _ip, C.POINTER(C.c_int64)]),
     "vep_plan_destroy": (None, [_p]),
     "vep_stream_open": (_i, [_p, _i, _i, _i, _i, _i]),
     "vep_stream_close": (_i, [_p, _i]),
+    "vep_set_staging_threads": (_i, [_p, _i]),
     "vep_submit": (_i, [_p, _i, C.POINTER(C.c_void_p * 3), C.POINTER(C.c_int32 * 3),
                         C.POINTER(FrameMeta), _i]),
     "vep_acquire_input": (_i, [_p, _i, C.POINTER(C.c_void_p * 3), C.POINTER(C.c_int32 * 3)]),
@@ -69,11 +72,14 @@ SIGNATURES = {
     "vep_tick_begin": (_i, [_p, _ip]),
     "vep_tick_wait": (_i, [_p]),
     "vep_tick": (_i, [_p, _ip]),
+    "vep_tick_begin_ticket": (_i, [_p, _ip, C.POINTER(C.c_uint64)]),
+    "vep_tick_wait_ticket": (_i, [_p, C.c_uint64]),
     "vep_result": (_i, [_p, _i, _pp, C.POINTER(C.c_size_t), _i32p]),
     "vep_result_packed": (_i, [_p, _i, _pp, C.POINTER(C.c_size_t)]),
     "vep_result_packed_at": (_i, [_p, _i, _i, _pp, C.POINTER(C.c_size_t)]),
     "vep_result_at": (_i, [_p, _i, _i, _pp, C.POINTER(C.c_size_t), _i32p]),
     "vep_result_device": (_i, [_p, _i, _pp, _i32p]),
+    "vep_result_device_pitched": (_i, [_p, _i, _pp, _i32p, _i32p]),
     "vep_videoframe_frame": (_i, [C.POINTER(FrameMeta), C.c_int32, C.c_int32, _p, _i32p, _p, _i32p]),
     "vep_get_stats": (_i, [_p, C.POINTER(Stats)]),
 }

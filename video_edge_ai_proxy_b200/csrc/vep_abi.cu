@@ -16,8 +16,13 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <condition_variable>
+#include <deque>
+#include <functional>
 #include <mutex>
 #include <new>
+#include <shared_mutex>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -75,13 +80,14 @@ struct Tables {
     std::vector<CtaWork> work;      // per-CTA table of the one-shot kernel
     int64_t alg_bytes = 0;
     int n_converted = 0;
-    int total_items = 0;            // item space of the persistent kernel
+    int total_items = 0;            // work items over all frames (0: nothing to launch)
     std::vector<int32_t> tick_cta_begin;   // tick kernel: first CTA of each frame, then the grid size
 };
 
 static inline bool aligned(const void *p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
 
-static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1, bool vec444_ok = false) {
+static int build_tables(const vep_frame_desc *d, int n, Tables &t) {
+    constexpr int rpt = vep::kTickRpt;
     if (n < 0 || (n > 0 && !d)) return fail(VEP_ERR_INVALID_ARG, "descs is null or n < 0");
     t.frames.clear();
     t.work.clear();
@@ -115,13 +121,15 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t, int rpt = 1, 
         f.y = s.plane[0]; f.c0 = gray ? s.plane[0] : s.plane[1]; f.c1 = (nv12 || gray) ? nullptr : s.plane[2]; f.dst = s.dst;
         f.sy = s.stride[0]; f.sc0 = gray ? s.stride[0] : s.stride[1]; f.sc1 = (nv12 || gray) ? 0 : s.stride[2]; f.sd = s.dst_stride;
         f.w = w; f.h = h; f.fmt = s.fmt;
+        // Vector path: every plane and the output 16-byte aligned (planar 8-bit chroma: 8) with strides that are
+        // multiples of the same.  Any even width qualifies for 8-bit samples: a stride that is a multiple of 16 and
+        // >= the row already contains the row rounded up to 16 bytes, which is all the last lane of a row reads.
         const size_t ca = (nv12 || bps == 2 || vep::fmt_is_444(s.fmt)) ? 16 : 8;
-        const bool vec = (w % 16 == 0) && aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
+        const bool vec = (bps == 1 || w % 16 == 0) && aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
                          (nv12 || gray || (aligned(f.c1, ca) && f.sc1 % ca == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
-        const bool bulk = vec && bps == 1 && (w % 32 == 0) && aligned(f.c0, 16) && f.sc0 % 16 == 0 && (nv12 || (aligned(f.c1, 16) && f.sc1 % 16 == 0));
-        f.fast = bulk ? vep::PATH_BULK : vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;
+        f.fast = vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;
         if (vep::fmt_vector_only_when_specialised(s.fmt))
-            f.fast = (f.fast != vep::PATH_GENERIC && homogeneous && vec444_ok) ? vep::PATH_VECTOR : vep::PATH_GENERIC;
+            f.fast = (f.fast != vep::PATH_GENERIC && homogeneous) ? vep::PATH_VECTOR : vep::PATH_GENERIC;
         // only the tick kernel has a vector path for 4:2:2, 4:4:4, gray and for 10-bit samples
         f.fast_tbl = (vep::fmt_is_422(s.fmt) || vep::fmt_vector_only_when_specialised(s.fmt) || bps == 2) ? vep::PATH_GENERIC : f.fast;
         f.segs = (w + vep::kSegPx - 1) / vep::kSegPx;
@@ -180,7 +188,10 @@ struct Slot {
 
 struct Stream {
     int id = 0, fmt = 0, w = 0, h = 0, ring = 1;
-    size_t off_c0 = 0, off_c1 = 0, in_bytes = 0, out_bytes = 0, in_slot = 0, out_slot = 0;
+    // staged planes (pinned and device alike) have rows padded to pitch_y / pitch_c so that every geometry meets the
+    // vector path's alignment; the device output has pitch_out (>= 3w, multiple of 16), the pinned output is tight
+    int pitch_y = 0, pitch_c = 0, pitch_out = 0;
+    size_t off_c0 = 0, off_c1 = 0, in_bytes = 0, out_bytes = 0, dev_out_bytes = 0, in_slot = 0, out_slot = 0, dev_out_slot = 0;
     std::vector<Slot> slots;
     int wr = 0;             // next slot to fill
     int newest = -1;        // newest READY slot
@@ -197,31 +208,64 @@ struct TickRec {
     std::vector<SlotRef> slots;
     cudaEvent_t k0 = nullptr, k1 = nullptr;
     bool active = false;
+    uint64_t ticket = 0;
 };
+
+// Helper threads for the staging copy of large frames (vep_submit): a 4K frame is 12-25 MB, one core copies
+// ~10-16 GB/s, a PCIe link takes 55 -- so frames above kBandSplitBytes are copied as row bands by the submitting
+// thread plus these workers.  They sleep on a condition variable otherwise.
+struct StagePool {
+    std::vector<std::thread> threads;
+    std::mutex mu;
+    std::condition_variable cv;
+    std::deque<std::function<void()>> q;
+    bool stop = false;
+    void start(int n) {
+        for (int i = 0; i < n; ++i)
+            threads.emplace_back([this] {
+                for (;;) {
+                    std::function<void()> job;
+                    {
+                        std::unique_lock<std::mutex> lk(mu);
+                        cv.wait(lk, [this] { return stop || !q.empty(); });
+                        if (q.empty()) return;
+                        job = std::move(q.front());
+                        q.pop_front();
+                    }
+                    job();
+                }
+            });
+    }
+    void post(std::function<void()> job) {
+        { std::lock_guard<std::mutex> lk(mu); q.push_back(std::move(job)); }
+        cv.notify_one();
+    }
+    void shutdown() {
+        { std::lock_guard<std::mutex> lk(mu); stop = true; }
+        cv.notify_all();
+        for (auto &t : threads) t.join();
+        threads.clear();
+    }
+};
+static constexpr size_t kBandSplitBytes = (size_t)4 << 20;
 
 struct vep_ctx {
     int device = 0;
-    int kernel = 2;              // 2: tick kernel, table in kernel params (default); 1: table-driven one-shot
-                                 // (VEP_KERNEL=oneshot; also the fallback beyond 128 frames); 0: VEP_KERNEL=persistent
-    int rpt = 2, minb = 4;       // tick kernel variant: row pairs per lane, min CTAs/SM (VEP_RPT, VEP_MINB)
-    int pdl = 1;                 // programmatic dependent launch attribute on tick launches (VEP_PDL=0 disables)
-    int specialize = 1;          // use the per-format instantiation for single-format launches (VEP_SPECIALIZE=0 disables)
-    int store_mode = 0;          // one-shot kernel only (VEP_STORE_MODE)
-    int resident_warps = 0;      // persistent kernel: warps the whole GPU keeps resident
     cudaStream_t main = nullptr;
     TableBuf tb[4];
     int tb_next = 0;
-    std::mutex mu;                                  // guards streams map, ticks, table buffers
+    std::shared_mutex smu;                          // guards the streams map (shared: lookups, exclusive: open/close)
+    std::mutex mu;                                  // guards ticks, table buffers, stats, scratch
     std::unordered_map<int, Stream *> streams;
     TickRec ticks[VEP_MAX_TICKS_IN_FLIGHT];
     int tick_head = 0, ticks_in_flight = 0;         // oldest in flight = tick_head
+    uint64_t next_ticket = 1, retired_ticket = 0;   // tickets are issued in order and retire in order
     vep_stats stats{};
     Tables scratch;
     std::vector<uint8_t> tick_blob;
+    StagePool pool;
+    int stage_threads = 0;                          // helpers besides the submitting thread
 };
-
-// 4:4:4 frames may take the vector path only where a format-specialised tick kernel will run them
-static inline bool vec444_ok(const vep_ctx *c) { return c->kernel == 2 && c->specialize && c->rpt == 2 && c->minb == 4; }
 
 struct vep_plan {
     vep_ctx *ctx = nullptr;
@@ -239,23 +283,16 @@ struct DeviceGuard {
     ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
 
-// grid of the persistent kernel: every warp gets the same number of items (no partial last round)
-static int persistent_ctas(const vep_ctx *c, int total_items) {
-    const int rounds = (total_items + c->resident_warps - 1) / c->resident_warps;
-    const int warps = (total_items + rounds - 1) / rounds;
-    return (warps + vep::kPWarps - 1) / vep::kPWarps;
-}
-
 // ---- tick kernel: descriptor table travels as a kernel parameter -------------------------------------
 static constexpr int kTickCapSmall = 16, kTickCapLarge = 128;
 
 template <int NF>
-static void fill_tick(const Tables &t, std::vector<uint8_t> &blob) {
+static void fill_tick(const Tables &t, std::vector<uint8_t> &blob, int wait_prior) {
     blob.assign(sizeof(vep::TickParams<NF>), 0);
     auto *P = reinterpret_cast<vep::TickParams<NF> *>(blob.data());
     const int n = t.n_converted;
     P->n_frames = n;
-    P->wait_prior = 1;
+    P->wait_prior = wait_prior;
     int per = n ? t.tick_cta_begin[1] - t.tick_cta_begin[0] : 0;
     for (int i = 1; i < n && per > 0; ++i) if (t.tick_cta_begin[i + 1] - t.tick_cta_begin[i] != per) per = 0;
     P->uniform_ctas = (n > 0 && n <= 65535) ? per : 0;
@@ -265,67 +302,55 @@ static void fill_tick(const Tables &t, std::vector<uint8_t> &blob) {
     for (int i = 0; i <= n; ++i) P->cta_begin[i] = t.tick_cta_begin[i];
     for (int i = 0; i < n; ++i) P->frames[i] = t.frames[i];
 }
+// TickParams::wait_prior for a launch order of the ABI
+static inline int wait_prior_of(int order) { return order == VEP_ORDER_NONE ? 0 : order == VEP_ORDER_WRITES ? 2 : 1; }
 // returns capacity used (0: does not fit -> caller falls back to the table-driven kernel)
-static int make_tick_blob(const Tables &t, std::vector<uint8_t> &blob, int *grid) {
+static int make_tick_blob(const Tables &t, std::vector<uint8_t> &blob, int *grid, int order = VEP_ORDER_STRICT) {
     const int n = t.n_converted;
     *grid = n ? t.tick_cta_begin[n] : 0;
-    if (n <= kTickCapSmall) { fill_tick<kTickCapSmall>(t, blob); return kTickCapSmall; }
-    if (n <= kTickCapLarge) { fill_tick<kTickCapLarge>(t, blob); return kTickCapLarge; }
+    if (n <= kTickCapSmall) { fill_tick<kTickCapSmall>(t, blob, wait_prior_of(order)); return kTickCapSmall; }
+    if (n <= kTickCapLarge) { fill_tick<kTickCapLarge>(t, blob, wait_prior_of(order)); return kTickCapLarge; }
     return 0;
 }
+// single-format launches run the instantiation in which the other formats' code is compiled out
 template <int NF>
-static const void *tick_kernel(int rpt, int minb, int only_fmt) {
-    if (rpt == 2 && minb == 4) {   // the default variant also exists specialised per pixel format
-        switch (only_fmt) {
-            case VEP_FMT_YUV420P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_YUV420P>;
-            case VEP_FMT_YUVJ420P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_YUVJ420P>;
-            case VEP_FMT_NV12: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_NV12>;
-            case VEP_FMT_NV21: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_NV21>;
-            case VEP_FMT_YUV422P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_YUV422P>;
-            case VEP_FMT_YUVJ422P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_YUVJ422P>;
-            case VEP_FMT_YUV420P10LE: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 3, vep::FMT_YUV420P10>;   // 80 registers: no spills
-            case VEP_FMT_YUV444P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 3, vep::FMT_YUV444P>;
-            case VEP_FMT_YUVJ444P: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 3, vep::FMT_YUVJ444P>;
-            case VEP_FMT_GRAY8: return (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4, vep::FMT_GRAY8>;
-            default: break;
-        }
+static const void *tick_kernel(int only_fmt) {
+    constexpr int R = vep::kTickRpt;
+    switch (only_fmt) {
+        case VEP_FMT_YUV420P: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_YUV420P>;
+        case VEP_FMT_YUVJ420P: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_YUVJ420P>;
+        case VEP_FMT_NV12: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_NV12>;
+        case VEP_FMT_NV21: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_NV21>;
+        case VEP_FMT_YUV422P: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_YUV422P>;
+        case VEP_FMT_YUVJ422P: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_YUVJ422P>;
+        case VEP_FMT_YUV420P10LE: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 3, vep::FMT_YUV420P10>;   // 80 registers: no spills
+        case VEP_FMT_YUV444P: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 3, vep::FMT_YUV444P>;
+        case VEP_FMT_YUVJ444P: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 3, vep::FMT_YUVJ444P>;
+        case VEP_FMT_GRAY8: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_GRAY8>;
+        default: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4>;
     }
-    if (rpt == 2) return minb >= 4 ? (const void *)vep::yuv_to_bgr24_tick<NF, 2, 4> : (const void *)vep::yuv_to_bgr24_tick<NF, 2, 3>;
-    if (minb >= 8) return (const void *)vep::yuv_to_bgr24_tick<NF, 1, 8>;
-    if (minb >= 6) return (const void *)vep::yuv_to_bgr24_tick<NF, 1, 6>;
-    return (const void *)vep::yuv_to_bgr24_tick<NF, 1, 5>;
 }
-static int launch_tick(const vep_ctx *c, int cap, const std::vector<uint8_t> &blob, int grid, cudaStream_t st) {
+static int launch_tick(int cap, const std::vector<uint8_t> &blob, int grid, cudaStream_t st) {
     if (grid <= 0) return VEP_OK;
-    const int32_t *hdr0 = reinterpret_cast<const int32_t *>(blob.data());   // n_frames, wait_prior, uniform_ctas, only_fmt
-    const int only = c->specialize ? hdr0[3] : -1;
-    const void *fn = cap == kTickCapSmall ? tick_kernel<kTickCapSmall>(c->rpt, c->minb, only) : tick_kernel<kTickCapLarge>(c->rpt, c->minb, only);
+    const int32_t *hdr = reinterpret_cast<const int32_t *>(blob.data());   // n_frames, wait_prior, uniform_ctas, only_fmt
+    const void *fn = cap == kTickCapSmall ? tick_kernel<kTickCapSmall>(hdr[3]) : tick_kernel<kTickCapLarge>(hdr[3]);
     void *args[1] = {const_cast<uint8_t *>(blob.data())};
     cudaLaunchConfig_t cfg{};
-    const int32_t *hdr = reinterpret_cast<const int32_t *>(blob.data());   // n_frames, wait_prior, uniform_ctas
     cfg.gridDim = hdr[2] > 0 ? dim3(hdr[2], hdr[0]) : dim3(grid);
     cfg.blockDim = dim3(vep::kThreads);
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = c->pdl ? 1 : 0;
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // programmatic dependent launch (see the kernel)
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     CUDA_TRY(cudaLaunchKernelExC(&cfg, fn, args));
     return VEP_OK;
 }
 
-static int launch_tables(const vep_ctx *c, const FrameDev *d_frames, const CtaWork *d_work, int n_ctas, int total_items, cudaStream_t st) {
+static int launch_tables(const FrameDev *d_frames, const CtaWork *d_work, int n_ctas, int total_items, cudaStream_t st) {
     if (total_items <= 0) return VEP_OK;
-    if (c->kernel == 0) {
-        vep::yuv_to_bgr24_persistent<<<persistent_ctas(c, total_items), vep::kPThreads, vep::kPSmemBytes, st>>>(d_frames, total_items);
-    } else {
-        switch (c->store_mode) {
-            case 1: vep::yuv_to_bgr24_batched<1><<<n_ctas, vep::kThreads, 0, st>>>(d_frames, d_work); break;
-            case 2: vep::yuv_to_bgr24_batched<2><<<n_ctas, vep::kThreads, 0, st>>>(d_frames, d_work); break;
-            default: vep::yuv_to_bgr24_batched<0><<<n_ctas, vep::kThreads, 0, st>>>(d_frames, d_work); break;
-        }
-    }
+    vep::yuv_to_bgr24_batched<<<n_ctas, vep::kThreads, 0, st>>>(d_frames, d_work);
     CUDA_TRY(cudaGetLastError());
     return VEP_OK;
 }
@@ -345,30 +370,21 @@ extern "C" int vep_create(int device, vep_ctx **out) {
     vep_ctx *c = new (std::nothrow) vep_ctx();
     if (!c) return fail(VEP_ERR_NOMEM, "out of host memory");
     c->device = device;
-    const char *sm = getenv("VEP_STORE_MODE");
-    c->store_mode = sm ? atoi(sm) : 0;
-    if (c->store_mode < 0 || c->store_mode > 2) c->store_mode = 0;
-    const char *kn = getenv("VEP_KERNEL");
-    c->kernel = !kn ? 2 : strcmp(kn, "persistent") == 0 ? 0 : strcmp(kn, "oneshot") == 0 ? 1 : 2;
-    const char *er = getenv("VEP_RPT"), *em = getenv("VEP_MINB");
-    c->rpt = (er && atoi(er) == 1) ? 1 : 2;
-    c->minb = em ? atoi(em) : (c->rpt == 2 ? 4 : 6);
-    const char *es = getenv("VEP_SPECIALIZE");
-    c->specialize = (es && atoi(es) == 0) ? 0 : 1;
-    const char *ep = getenv("VEP_PDL");
-    c->pdl = (ep && atoi(ep) == 0) ? 0 : 1;
-    CUDA_TRY(cudaFuncSetAttribute(vep::yuv_to_bgr24_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, vep::kPSmemBytes));
-    CUDA_TRY(cudaFuncSetAttribute(vep::yuv_to_bgr24_persistent, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    int per_sm = 0;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, vep::yuv_to_bgr24_persistent, vep::kPThreads, vep::kPSmemBytes));
-    if (per_sm < 1) return fail(VEP_ERR_CUDA, "persistent kernel does not fit on an SM");
-    const char *occ = getenv("VEP_CTAS_PER_SM");
-    if (occ && atoi(occ) >= 1 && atoi(occ) < per_sm) per_sm = atoi(occ);
-    c->resident_warps = per_sm * prop.multiProcessorCount * vep::kPWarps;
     CUDA_TRY(cudaStreamCreateWithFlags(&c->main, cudaStreamNonBlocking));
     for (auto &t : c->tb) CUDA_TRY(cudaEventCreateWithFlags(&t.used, cudaEventDisableTiming));
     for (auto &t : c->ticks) { CUDA_TRY(cudaEventCreate(&t.k0)); CUDA_TRY(cudaEventCreate(&t.k1)); }
     *out = c;
+    return VEP_OK;
+}
+
+extern "C" int vep_set_staging_threads(vep_ctx *c, int n) {
+    if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
+    if (n < 0 || n > 64) return fail(VEP_ERR_INVALID_ARG, "staging threads %d outside [0,64]", n);
+    std::lock_guard<std::mutex> lk(c->mu);
+    c->pool.shutdown();
+    c->pool.stop = false;
+    c->stage_threads = n;
+    if (n) c->pool.start(n);
     return VEP_OK;
 }
 
@@ -387,6 +403,7 @@ static void free_stream(Stream *s) {
 extern "C" void vep_destroy(vep_ctx *c) {
     if (!c) return;
     DeviceGuard g(c->device);
+    c->pool.shutdown();
     if (c->main) cudaStreamSynchronize(c->main);
     for (auto &kv : c->streams) free_stream(kv.second);
     for (auto &t : c->tb) { if (t.h) cudaFreeHost(t.h); if (t.d) cudaFree(t.d); if (t.used) cudaEventDestroy(t.used); }
@@ -395,18 +412,16 @@ extern "C" void vep_destroy(vep_ctx *c) {
     delete c;
 }
 
-// upload `t` through the next ring buffer and launch on `st`
-static int upload_and_launch(vep_ctx *c, const Tables &t, cudaStream_t st) {
+// launch `t` on `st`: up to 128 frames ride in the kernel parameters, larger batches go through the upload ring
+static int upload_and_launch(vep_ctx *c, const Tables &t, cudaStream_t st, int order) {
     if (t.total_items == 0) return VEP_OK;
-    if (c->kernel == 2) {
-        int grid = 0;
-        const int cap = make_tick_blob(t, c->tick_blob, &grid);
-        if (cap) {   // cudaLaunchKernel copies the parameter block before returning: the blob is reusable at once
-            int rc = launch_tick(c, cap, c->tick_blob, grid, st);
-            if (rc) return rc;
-            c->stats.kernel_launches++;
-            return VEP_OK;
-        }
+    int grid = 0;
+    const int cap = make_tick_blob(t, c->tick_blob, &grid, order);
+    if (cap) {   // cudaLaunchKernel copies the parameter block before returning: the blob is reusable at once
+        int rc = launch_tick(cap, c->tick_blob, grid, st);
+        if (rc) return rc;
+        c->stats.kernel_launches++;
+        return VEP_OK;
     }
     TableBuf &b = c->tb[c->tb_next];
     c->tb_next = (c->tb_next + 1) % 4;
@@ -426,7 +441,7 @@ static int upload_and_launch(vep_ctx *c, const Tables &t, cudaStream_t st) {
     memcpy(b.h, t.frames.data(), t.frames.size() * sizeof(FrameDev));
     memcpy((char *)b.h + fb, t.work.data(), t.work.size() * sizeof(CtaWork));
     CUDA_TRY(cudaMemcpyAsync(b.d, b.h, need, cudaMemcpyHostToDevice, st));
-    int rc = launch_tables(c, (const FrameDev *)b.d, (const CtaWork *)((char *)b.d + fb), (int)t.work.size(), t.total_items, st);
+    int rc = launch_tables((const FrameDev *)b.d, (const CtaWork *)((char *)b.d + fb), (int)t.work.size(), t.total_items, st);
     if (rc) return rc;
     CUDA_TRY(cudaEventRecord(b.used, st));
     b.pending = true;
@@ -434,16 +449,20 @@ static int upload_and_launch(vep_ctx *c, const Tables &t, cudaStream_t st) {
     return VEP_OK;
 }
 
-extern "C" int vep_convert_batch(vep_ctx *c, const vep_frame_desc *descs, int n, void *cuda_stream) {
+extern "C" int vep_convert_batch_ordered(vep_ctx *c, const vep_frame_desc *descs, int n, void *cuda_stream, int order) {
     if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
+    if (order < VEP_ORDER_STRICT || order > VEP_ORDER_NONE) return fail(VEP_ERR_INVALID_ARG, "unknown launch order %d", order);
     DeviceGuard g(c->device);
     std::lock_guard<std::mutex> lk(c->mu);
-    int rc = build_tables(descs, n, c->scratch, c->rpt, vec444_ok(c));
+    int rc = build_tables(descs, n, c->scratch);
     if (rc) return rc;
-    rc = upload_and_launch(c, c->scratch, (cudaStream_t)cuda_stream);
+    rc = upload_and_launch(c, c->scratch, (cudaStream_t)cuda_stream, order);
     if (rc) return rc;
     c->stats.frames_converted += c->scratch.n_converted;
     return VEP_OK;
+}
+extern "C" int vep_convert_batch(vep_ctx *c, const vep_frame_desc *descs, int n, void *cuda_stream) {
+    return vep_convert_batch_ordered(c, descs, n, cuda_stream, VEP_ORDER_STRICT);
 }
 
 extern "C" int vep_plan_create(vep_ctx *c, const vep_frame_desc *descs, int n, vep_plan **out) {
@@ -451,27 +470,25 @@ extern "C" int vep_plan_create(vep_ctx *c, const vep_frame_desc *descs, int n, v
     *out = nullptr;
     DeviceGuard g(c->device);
     Tables t;
-    int rc = build_tables(descs, n, t, c->rpt, vec444_ok(c));
+    int rc = build_tables(descs, n, t);
     if (rc) return rc;
     vep_plan *p = new (std::nothrow) vep_plan();
     if (!p) return fail(VEP_ERR_NOMEM, "out of host memory");
     p->ctx = c;
-    p->n_ctas = c->kernel == 0 ? (t.total_items ? persistent_ctas(c, t.total_items) : 0) : (int)t.work.size();
     p->total_items = t.total_items;
     p->n_converted = t.n_converted;
-    if (c->kernel == 2) {
-        p->tick_cap = make_tick_blob(t, p->tick_blob, &p->tick_grid);
-        if (p->tick_cap) {
-            p->n_ctas = p->tick_grid;
-            p->tick_blob_overlap = p->tick_blob;
-            reinterpret_cast<int32_t *>(p->tick_blob_overlap.data())[1] = 0;   // TickParams::wait_prior
-            p->tick_blob_writes = p->tick_blob;
-            reinterpret_cast<int32_t *>(p->tick_blob_writes.data())[1] = 2;
-        }
-        else p->n_ctas = (int)t.work.size();
+    p->tick_cap = make_tick_blob(t, p->tick_blob, &p->tick_grid);
+    if (p->tick_cap) {
+        p->n_ctas = p->tick_grid;
+        p->tick_blob_overlap = p->tick_blob;
+        reinterpret_cast<int32_t *>(p->tick_blob_overlap.data())[1] = wait_prior_of(VEP_ORDER_NONE);   // TickParams::wait_prior
+        p->tick_blob_writes = p->tick_blob;
+        reinterpret_cast<int32_t *>(p->tick_blob_writes.data())[1] = wait_prior_of(VEP_ORDER_WRITES);
+    } else {
+        p->n_ctas = (int)t.work.size();
     }
     p->alg_bytes = t.alg_bytes;
-    if (t.total_items) {
+    if (t.total_items && !p->tick_cap) {   // more than 128 frames: the table-driven kernel reads its tables from device memory
         cudaError_t e = cudaMalloc(&p->d_frames, t.frames.size() * sizeof(FrameDev));
         if (e == cudaSuccess) e = cudaMalloc(&p->d_work, t.work.size() * sizeof(CtaWork));
         if (e == cudaSuccess) e = cudaMemcpy(p->d_frames, t.frames.data(), t.frames.size() * sizeof(FrameDev), cudaMemcpyHostToDevice);
@@ -487,21 +504,42 @@ extern "C" int vep_plan_create(vep_ctx *c, const vep_frame_desc *descs, int n, v
     return VEP_OK;
 }
 
+static int plan_enqueue(vep_plan *p, cudaStream_t st, int order) {
+    const std::vector<uint8_t> &blob = order == VEP_ORDER_NONE ? p->tick_blob_overlap : order == VEP_ORDER_WRITES ? p->tick_blob_writes : p->tick_blob;
+    return p->tick_cap ? launch_tick(p->tick_cap, blob, p->tick_grid, st) : launch_tables(p->d_frames, p->d_work, p->n_ctas, p->total_items, st);
+}
 static int plan_launch(vep_plan *p, void *cuda_stream, int order) {
     if (!p) return fail(VEP_ERR_INVALID_ARG, "plan is null");
     if (order < VEP_ORDER_STRICT || order > VEP_ORDER_NONE) return fail(VEP_ERR_INVALID_ARG, "unknown launch order %d", order);
     DeviceGuard g(p->ctx->device);
-    const std::vector<uint8_t> &blob = order == VEP_ORDER_NONE ? p->tick_blob_overlap : order == VEP_ORDER_WRITES ? p->tick_blob_writes : p->tick_blob;
-    int rc = p->tick_cap ? launch_tick(p->ctx, p->tick_cap, blob, p->tick_grid, (cudaStream_t)cuda_stream)
-                         : launch_tables(p->ctx, p->d_frames, p->d_work, p->n_ctas, p->total_items, (cudaStream_t)cuda_stream);
+    int rc = plan_enqueue(p, (cudaStream_t)cuda_stream, order);
     if (rc) return rc;
-    p->ctx->stats.kernel_launches++;
-    p->ctx->stats.frames_converted += p->n_converted;
+    __atomic_add_fetch(&p->ctx->stats.kernel_launches, 1, __ATOMIC_RELAXED);
+    __atomic_add_fetch(&p->ctx->stats.frames_converted, (int64_t)p->n_converted, __ATOMIC_RELAXED);
     return VEP_OK;
 }
 extern "C" int vep_plan_launch(vep_plan *p, void *cuda_stream) { return plan_launch(p, cuda_stream, VEP_ORDER_STRICT); }
 extern "C" int vep_plan_launch_overlapped(vep_plan *p, void *cuda_stream) { return plan_launch(p, cuda_stream, VEP_ORDER_NONE); }
 extern "C" int vep_plan_launch_ordered(vep_plan *p, void *cuda_stream, int order) { return plan_launch(p, cuda_stream, order); }
+
+// A run of launches issued from native code in one call: what a C producer that converts tick after tick does, and
+// what the benchmark uses so that the Python call overhead per launch stays out of a short timed region.
+extern "C" int vep_plan_launch_sequence(vep_plan *const *plans, int n, void *cuda_stream, int order) {
+    if (n < 0 || (n > 0 && !plans)) return fail(VEP_ERR_INVALID_ARG, "plans is null or n < 0");
+    if (order < VEP_ORDER_STRICT || order > VEP_ORDER_NONE) return fail(VEP_ERR_INVALID_ARG, "unknown launch order %d", order);
+    for (int i = 0; i < n; ++i) if (!plans[i]) return fail(VEP_ERR_INVALID_ARG, "plans[%d] is null", i);
+    if (n == 0) return VEP_OK;
+    DeviceGuard g(plans[0]->ctx->device);
+    for (int i = 0; i < n; ++i) {
+        vep_plan *p = plans[i];
+        if (p->ctx->device != plans[0]->ctx->device) return fail(VEP_ERR_INVALID_ARG, "plans[%d] belongs to another device", i);
+        int rc = plan_enqueue(p, (cudaStream_t)cuda_stream, order);
+        if (rc) return rc;
+        __atomic_add_fetch(&p->ctx->stats.kernel_launches, 1, __ATOMIC_RELAXED);
+        __atomic_add_fetch(&p->ctx->stats.frames_converted, (int64_t)p->n_converted, __ATOMIC_RELAXED);
+    }
+    return VEP_OK;
+}
 
 extern "C" int vep_plan_info(const vep_plan *p, int *n_converted, int *n_ctas, int64_t *alg_bytes) {
     if (!p) return fail(VEP_ERR_INVALID_ARG, "plan is null");
@@ -579,10 +617,14 @@ extern "C" int vep_videoframe_frame(const vep_frame_meta *m, int32_t width, int3
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 static Stream *find_stream(vep_ctx *c, int id) {
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::shared_lock<std::shared_mutex> lk(c->smu);
     auto it = c->streams.find(id);
     return it == c->streams.end() ? nullptr : it->second;
 }
+
+// row pitch of a staged plane / of the device output: tight when that already is a multiple of 16 bytes (every
+// common resolution), else padded to 64 so that widths like 854 or 1366 keep the kernels' vector path
+static inline int pitch_of(size_t row_bytes) { return (int)(row_bytes % 16 == 0 ? row_bytes : align_up(row_bytes, 64)); }
 
 extern "C" int vep_stream_open(vep_ctx *c, int stream_id, int fmt, int w, int h, int ring_depth) {
     if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
@@ -593,31 +635,37 @@ extern "C" int vep_stream_open(vep_ctx *c, int stream_id, int fmt, int w, int h,
     if (ring_depth > 64) return fail(VEP_ERR_INVALID_ARG, "ring_depth %d > 64", ring_depth);
     DeviceGuard g(c->device);
     {
-        std::lock_guard<std::mutex> lk(c->mu);
+        std::shared_lock<std::shared_mutex> lk(c->smu);
         if (c->streams.count(stream_id)) return fail(VEP_ERR_STATE, "stream %d already open", stream_id);
     }
     Stream *s = new (std::nothrow) Stream();
     if (!s) return fail(VEP_ERR_NOMEM, "out of host memory");
     s->id = stream_id; s->fmt = fmt; s->w = w; s->h = h; s->ring = ring_depth;
     const size_t bps = vep::fmt_bytes_per_sample(fmt);
-    const size_t ysz = (size_t)w * h * bps;       // bytes of the luma plane (chroma planes scale with it)
+    const bool semi = vep::fmt_is_semiplanar(fmt), gray = fmt == VEP_FMT_GRAY8;
+    const size_t crow = ((semi || vep::fmt_is_444(fmt)) ? (size_t)w : (size_t)w / 2) * bps;   // bytes per chroma row
+    const size_t crows = (vep::fmt_is_422(fmt) || vep::fmt_is_444(fmt)) ? (size_t)h : (size_t)h / 2;
+    s->pitch_y = pitch_of((size_t)w * bps);
+    s->pitch_c = gray ? 0 : pitch_of(crow);
+    s->pitch_out = pitch_of((size_t)w * 3);
+    const size_t ysz = (size_t)s->pitch_y * h, csz = (size_t)s->pitch_c * crows;
     s->off_c0 = align_up(ysz, 256);
-    const size_t csz = vep::fmt_is_444(fmt) ? ysz : vep::fmt_is_422(fmt) ? ysz / 2 : ysz / 4;   // bytes of one planar chroma plane
-    if (fmt == VEP_FMT_GRAY8) { s->off_c0 = s->off_c1 = 0; s->in_bytes = ysz; }
-    else if (vep::fmt_is_semiplanar(fmt)) { s->off_c1 = 0; s->in_bytes = s->off_c0 + ysz / 2; }
+    if (gray) { s->off_c0 = s->off_c1 = 0; s->in_bytes = ysz; }
+    else if (semi) { s->off_c1 = 0; s->in_bytes = s->off_c0 + csz; }
     else { s->off_c1 = s->off_c0 + align_up(csz, 256); s->in_bytes = s->off_c1 + csz; }
     s->out_bytes = (size_t)w * h * 3;
+    s->dev_out_bytes = (size_t)s->pitch_out * h;
     s->in_slot = align_up(s->in_bytes, 4096);
     s->out_slot = align_up(kHdrRoom + s->out_bytes + kTrailerRoom, 4096);
+    s->dev_out_slot = align_up(s->dev_out_bytes, 4096);
     const int ns = ring_depth + VEP_MAX_TICKS_IN_FLIGHT + 2;   // ring + ticks in flight + one filling + slack
     s->slots.resize(ns);
-    // input staging is written by the CPU (streaming stores) and read by the DMA engine; write-combined pinned
-    // memory (VEP_WC=1) measured the same end to end as ordinary pinned memory on the B200 host, so it stays
-    // opt-in (a caller that reads back a slot obtained from vep_acquire_input would crawl on WC memory)
-    static const bool wc = getenv("VEP_WC") && atoi(getenv("VEP_WC")) == 1;
+    // Input staging is written by the CPU (streaming stores) and read by the DMA engine.  Write-combined pinned
+    // memory measured the same end to end as ordinary pinned memory on the B200 host (round 1), and a caller that
+    // reads back a slot obtained from vep_acquire_input would crawl on it, so ordinary pinned memory is used.
     cudaError_t e = cudaHostAlloc((void **)&s->h_base, s->out_slot * ns, cudaHostAllocDefault);
-    if (e == cudaSuccess) e = cudaHostAlloc((void **)&s->h_in_base, s->in_slot * ns, wc ? cudaHostAllocWriteCombined : cudaHostAllocDefault);
-    if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_base, (s->in_slot + s->out_slot) * ns);
+    if (e == cudaSuccess) e = cudaHostAlloc((void **)&s->h_in_base, s->in_slot * ns, cudaHostAllocDefault);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&s->d_base, (s->in_slot + s->dev_out_slot) * ns);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->cs_in, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->cs_out, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s->ev_in, cudaEventDisableTiming);
@@ -625,15 +673,22 @@ extern "C" int vep_stream_open(vep_ctx *c, int stream_id, int fmt, int w, int h,
         Slot &sl = s->slots[i];
         sl.h_in = s->h_in_base + s->in_slot * i;
         sl.h_out = s->h_base + s->out_slot * i;
-        sl.d_in = s->d_base + (s->in_slot + s->out_slot) * i;
+        sl.d_in = s->d_base + (s->in_slot + s->dev_out_slot) * i;
         sl.d_out = sl.d_in + s->in_slot;
         e = cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming);
     }
+    // padded rows: the padding is read by the last lane of a row (never used); give it defined contents once
+    if (e == cudaSuccess && s->pitch_y != (int)(w * bps)) memset(s->h_in_base, 0, s->in_slot * ns);
     if (e != cudaSuccess) {
         free_stream(s);
         return fail(e == cudaErrorMemoryAllocation ? VEP_ERR_NOMEM : VEP_ERR_CUDA, "stream_open: %s", cudaGetErrorString(e));
     }
-    std::lock_guard<std::mutex> lk(c->mu);
+    std::unique_lock<std::shared_mutex> lk(c->smu);
+    if (c->streams.count(stream_id)) {
+        lk.unlock();
+        free_stream(s);
+        return fail(VEP_ERR_STATE, "stream %d already open", stream_id);
+    }
     c->streams[stream_id] = s;
     return VEP_OK;
 }
@@ -643,8 +698,9 @@ extern "C" int vep_stream_close(vep_ctx *c, int stream_id) {
     DeviceGuard g(c->device);
     Stream *s = nullptr;
     {
-        std::lock_guard<std::mutex> lk(c->mu);
+        std::lock_guard<std::mutex> tk(c->mu);
         if (c->ticks_in_flight) return fail(VEP_ERR_BUSY, "ticks in flight; call vep_tick_wait first");
+        std::unique_lock<std::shared_mutex> lk(c->smu);
         auto it = c->streams.find(stream_id);
         if (it == c->streams.end()) return fail(VEP_ERR_INVALID_ARG, "stream %d not open", stream_id);
         s = it->second;
@@ -668,12 +724,10 @@ static int claim_slot(Stream *s) {
     return s->wr;
 }
 
-static void plane_ptrs(Stream *s, uint8_t *base, uint8_t *pl[3], int32_t st[3]) {
+static void plane_ptrs(const Stream *s, uint8_t *base, uint8_t *pl[3], int32_t st[3]) {
     const bool semi = vep::fmt_is_semiplanar(s->fmt);
-    const int bps = vep::fmt_bytes_per_sample(s->fmt);
-    const int cwp = vep::fmt_is_444(s->fmt) ? s->w : s->w / 2;     // planar chroma samples per row
     pl[0] = base; pl[1] = base + s->off_c0; pl[2] = semi ? nullptr : base + s->off_c1;
-    st[0] = s->w * bps; st[1] = semi ? s->w : cwp * bps; st[2] = semi ? 0 : cwp * bps;
+    st[0] = s->pitch_y; st[1] = s->pitch_c; st[2] = semi ? 0 : s->pitch_c;
     if (s->fmt == VEP_FMT_GRAY8) { pl[1] = pl[2] = nullptr; st[1] = st[2] = 0; }
 }
 
@@ -725,10 +779,41 @@ static void stream_copy(uint8_t *dst, const uint8_t *src, size_t n) {
     static const bool avx2 = __builtin_cpu_supports("avx2");
     if (avx2 && n >= 4096) stream_copy_avx2(dst, src, n); else memcpy(dst, src, n);
 }
-static void copy_plane(uint8_t *dst, int dstride, const uint8_t *src, int sstride, int row_bytes, int rows) {
-    if (dstride == sstride && sstride == row_bytes) stream_copy(dst, src, (size_t)row_bytes * rows);
-    else for (int r = 0; r < rows; ++r) stream_copy(dst + (size_t)r * dstride, src + (size_t)r * sstride, row_bytes);
+static void copy_rows(uint8_t *dst, int dstride, const uint8_t *src, int sstride, int row_bytes, int r0, int r1) {
+    if (dstride == sstride && sstride == row_bytes) stream_copy(dst + (size_t)r0 * dstride, src + (size_t)r0 * sstride, (size_t)row_bytes * (r1 - r0));
+    else for (int r = r0; r < r1; ++r) stream_copy(dst + (size_t)r * dstride, src + (size_t)r * sstride, row_bytes);
     _mm_sfence();   // order the streaming stores before the commit that makes the slot visible
+}
+
+struct PlaneCopy { uint8_t *dst; int dstride; const uint8_t *src; int sstride, row_bytes, rows; };
+
+// copy up to three planes; large frames are cut into row bands shared with the context's helper threads
+static void stage_planes(vep_ctx *c, const PlaneCopy *pc, int n_planes) {
+    size_t total = 0;
+    for (int i = 0; i < n_planes; ++i) total += (size_t)pc[i].row_bytes * pc[i].rows;
+    const int helpers = c->stage_threads;
+    if (helpers == 0 || total < kBandSplitBytes) {
+        for (int i = 0; i < n_planes; ++i) copy_rows(pc[i].dst, pc[i].dstride, pc[i].src, pc[i].sstride, pc[i].row_bytes, 0, pc[i].rows);
+        return;
+    }
+    const int parts = helpers + 1;
+    struct Join { std::mutex mu; std::condition_variable cv; int left; } join;
+    join.left = helpers;
+    auto band = [pc, n_planes, parts](int k) {
+        for (int i = 0; i < n_planes; ++i) {
+            const int r0 = (int)((int64_t)pc[i].rows * k / parts), r1 = (int)((int64_t)pc[i].rows * (k + 1) / parts);
+            if (r1 > r0) copy_rows(pc[i].dst, pc[i].dstride, pc[i].src, pc[i].sstride, pc[i].row_bytes, r0, r1);
+        }
+    };
+    for (int k = 1; k < parts; ++k)
+        c->pool.post([&join, band, k] {
+            band(k);
+            std::lock_guard<std::mutex> lk(join.mu);
+            if (--join.left == 0) join.cv.notify_one();
+        });
+    band(0);
+    std::unique_lock<std::mutex> lk(join.mu);
+    join.cv.wait(lk, [&join] { return join.left == 0; });
 }
 
 extern "C" int vep_submit(vep_ctx *c, int stream_id, const uint8_t *const plane[3], const int32_t stride[3],
@@ -755,9 +840,12 @@ extern "C" int vep_submit(vep_ctx *c, int stream_id, const uint8_t *const plane[
         plane_ptrs(s, s->slots[i].h_in, pl, st);
     }
     // the copy runs outside the lock: one producer per stream
-    copy_plane(pl[0], st[0], plane[0], stride[0], s->w * bps, s->h);
-    if (!gray) copy_plane(pl[1], st[1], plane[1], stride[1], cw, crows);
-    if (!semi && !gray) copy_plane(pl[2], st[2], plane[2], stride[2], cw, crows);
+    PlaneCopy pc[3];
+    int np = 0;
+    pc[np++] = PlaneCopy{pl[0], st[0], plane[0], stride[0], s->w * bps, s->h};
+    if (!gray) pc[np++] = PlaneCopy{pl[1], st[1], plane[1], stride[1], cw, crows};
+    if (!semi && !gray) pc[np++] = PlaneCopy{pl[2], st[2], plane[2], stride[2], cw, crows};
+    stage_planes(c, pc, np);
     return vep_commit_input(c, stream_id, meta);
 }
 
@@ -773,15 +861,17 @@ static void write_framing(Stream *s, Slot &sl) {
 
 static int tick_enqueue(vep_ctx *c, TickRec &t, int *n_frames);
 
-extern "C" int vep_tick_begin(vep_ctx *c, int *n_frames) {
+extern "C" int vep_tick_begin_ticket(vep_ctx *c, int *n_frames, uint64_t *ticket) {
     if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
     if (n_frames) *n_frames = 0;
+    if (ticket) *ticket = 0;
     DeviceGuard g(c->device);
     std::lock_guard<std::mutex> lk(c->mu);
     if (c->ticks_in_flight >= VEP_MAX_TICKS_IN_FLIGHT) return fail(VEP_ERR_BUSY, "%d ticks already in flight; call vep_tick_wait", VEP_MAX_TICKS_IN_FLIGHT);
     TickRec &t = c->ticks[(c->tick_head + c->ticks_in_flight) % VEP_MAX_TICKS_IN_FLIGHT];
     t.slots.clear();
-    const int rc = tick_enqueue(c, t, n_frames);
+    int nf = 0;
+    const int rc = tick_enqueue(c, t, &nf);
     if (rc != VEP_OK) {
         // a CUDA call failed half-way: the frames of this tick are dropped (the reference drops a frame on any
         // exception, read_image.py:130-131) and their slots are released so the cameras are not wedged
@@ -792,13 +882,20 @@ extern "C" int vep_tick_begin(vep_ctx *c, int *n_frames) {
             r.s->slots[r.slot].state = SLOT_FREE;
         }
         t.slots.clear();
+        return rc;
     }
-    return rc;
+    if (n_frames) *n_frames = nf;
+    // an empty tick starts nothing; its ticket is that of the newest real tick, so waiting for it still means
+    // "everything begun before this call has landed"
+    if (ticket) *ticket = nf ? t.ticket : c->next_ticket - 1;
+    return VEP_OK;
 }
+extern "C" int vep_tick_begin(vep_ctx *c, int *n_frames) { return vep_tick_begin_ticket(c, n_frames, nullptr); }
 
 static int tick_enqueue(vep_ctx *c, TickRec &t, int *n_frames) {
     std::vector<vep_frame_desc> descs;
     std::vector<Stream *> involved;
+    std::shared_lock<std::shared_mutex> map_lk(c->smu);
     // 1. H2D of every committed frame on its camera's input stream
     for (auto &kv : c->streams) {
         Stream *s = kv.second;
@@ -813,13 +910,10 @@ static int tick_enqueue(vep_ctx *c, TickRec &t, int *n_frames) {
             CUDA_TRY(cudaMemcpyAsync(sl.d_in, sl.h_in, s->in_bytes, cudaMemcpyHostToDevice, s->cs_in));
             c->stats.h2d_bytes += (int64_t)s->in_bytes;
             vep_frame_desc d{};
-            const bool semi = vep::fmt_is_semiplanar(s->fmt);
-            const int bps = vep::fmt_bytes_per_sample(s->fmt);
-            d.plane[0] = sl.d_in; d.plane[1] = sl.d_in + s->off_c0; d.plane[2] = semi ? nullptr : sl.d_in + s->off_c1;
-            const int cwp = vep::fmt_is_444(s->fmt) ? s->w : s->w / 2;
-            d.stride[0] = s->w * bps; d.stride[1] = semi ? s->w : cwp * bps; d.stride[2] = semi ? 0 : cwp * bps;
-            if (s->fmt == VEP_FMT_GRAY8) { d.plane[1] = d.plane[2] = nullptr; d.stride[1] = d.stride[2] = 0; }
-            d.dst = sl.d_out; d.dst_stride = 3 * s->w; d.width = s->w; d.height = s->h; d.fmt = s->fmt; d.convert = 1;
+            uint8_t *pl[3];
+            plane_ptrs(s, sl.d_in, pl, d.stride);
+            d.plane[0] = pl[0]; d.plane[1] = pl[1]; d.plane[2] = pl[2];
+            d.dst = sl.d_out; d.dst_stride = s->pitch_out; d.width = s->w; d.height = s->h; d.fmt = s->fmt; d.convert = 1;
             descs.push_back(d);
             write_framing(s, sl);
             sl.state = SLOT_INFLIGHT;
@@ -833,22 +927,30 @@ static int tick_enqueue(vep_ctx *c, TickRec &t, int *n_frames) {
         }
     }
     if (t.slots.empty()) return VEP_OK;
-    // 2. one batched launch for the whole tick
-    int rc = build_tables(descs.data(), (int)descs.size(), c->scratch, c->rpt, vec444_ok(c));
+    // 2. one batched launch for the whole tick.  Its inputs come from the copies above and its outputs are slots no
+    //    earlier tick still owns, so it needs no ordering against the previous tick's kernel (VEP_ORDER_NONE): with
+    //    programmatic dependent launch it may start while that kernel drains.
+    int rc = build_tables(descs.data(), (int)descs.size(), c->scratch);
     if (rc) return rc;
     CUDA_TRY(cudaEventRecord(t.k0, c->main));
-    rc = upload_and_launch(c, c->scratch, c->main);
+    rc = upload_and_launch(c, c->scratch, c->main, VEP_ORDER_NONE);
     if (rc) return rc;
     CUDA_TRY(cudaEventRecord(t.k1, c->main));
-    // 3. D2H of each result on its camera's output stream, payload lands behind the wire prefix
+    // 3. D2H of each result on its camera's output stream, payload lands behind the wire prefix; a padded device
+    //    pitch (width*3 not a multiple of 16) is removed by the copy engine on the way out
     for (Stream *s : involved) CUDA_TRY(cudaStreamWaitEvent(s->cs_out, t.k1, 0));
     for (auto &r : t.slots) {
-        Slot &sl = r.s->slots[r.slot];
-        CUDA_TRY(cudaMemcpyAsync(sl.h_out + kHdrRoom, sl.d_out, r.s->out_bytes, cudaMemcpyDeviceToHost, r.s->cs_out));
-        CUDA_TRY(cudaEventRecord(sl.done, r.s->cs_out));
-        c->stats.d2h_bytes += (int64_t)r.s->out_bytes;
+        Stream *s = r.s;
+        Slot &sl = s->slots[r.slot];
+        if ((size_t)s->pitch_out == (size_t)s->w * 3)
+            CUDA_TRY(cudaMemcpyAsync(sl.h_out + kHdrRoom, sl.d_out, s->out_bytes, cudaMemcpyDeviceToHost, s->cs_out));
+        else
+            CUDA_TRY(cudaMemcpy2DAsync(sl.h_out + kHdrRoom, (size_t)s->w * 3, sl.d_out, s->pitch_out, (size_t)s->w * 3, s->h, cudaMemcpyDeviceToHost, s->cs_out));
+        CUDA_TRY(cudaEventRecord(sl.done, s->cs_out));
+        c->stats.d2h_bytes += (int64_t)s->out_bytes;
     }
     t.active = true;
+    t.ticket = c->next_ticket++;
     c->ticks_in_flight++;
     c->stats.ticks++;
     c->stats.frames_converted += (int64_t)t.slots.size();
@@ -856,32 +958,59 @@ static int tick_enqueue(vep_ctx *c, TickRec &t, int *n_frames) {
     return VEP_OK;
 }
 
+// Retire ticks, oldest first, up to and including `upto` (UINT64_MAX: only the oldest one).  The event waits run
+// without the context lock, so producers keep staging and other threads keep beginning ticks meanwhile.
+static int retire_ticks(vep_ctx *c, uint64_t upto, bool only_oldest) {
+    DeviceGuard g(c->device);
+    for (;;) {
+        std::vector<cudaEvent_t> evs;
+        uint64_t id = 0;
+        {
+            std::lock_guard<std::mutex> lk(c->mu);
+            if (!c->ticks_in_flight) return VEP_OK;
+            TickRec &t = c->ticks[c->tick_head];
+            if (!only_oldest && t.ticket > upto) return VEP_OK;
+            id = t.ticket;
+            for (auto &r : t.slots) evs.push_back(r.s->slots[r.slot].done);
+        }
+        for (cudaEvent_t e : evs) CUDA_TRY(cudaEventSynchronize(e));
+        {
+            std::lock_guard<std::mutex> lk(c->mu);
+            TickRec &t = c->ticks[c->tick_head];
+            if (c->ticks_in_flight && t.ticket == id) {     // else another waiter retired it meanwhile
+                float ms = 0.f;
+                if (cudaEventElapsedTime(&ms, t.k0, t.k1) == cudaSuccess) c->stats.last_kernel_ms = ms;
+                for (auto &r : t.slots) {
+                    std::lock_guard<std::mutex> sl_lk(r.s->mu);
+                    r.s->slots[r.slot].state = SLOT_READY;
+                    r.s->newest = r.slot;
+                    r.s->n_ready++;
+                }
+                t.slots.clear();
+                t.active = false;
+                c->retired_ticket = id;
+                c->tick_head = (c->tick_head + 1) % VEP_MAX_TICKS_IN_FLIGHT;
+                c->ticks_in_flight--;
+            }
+        }
+        if (only_oldest) return VEP_OK;
+    }
+}
+
 extern "C" int vep_tick_wait(vep_ctx *c) {
     if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
-    DeviceGuard g(c->device);
-    std::lock_guard<std::mutex> lk(c->mu);
-    if (!c->ticks_in_flight) return VEP_OK;
-    TickRec &t = c->ticks[c->tick_head];
-    for (auto &r : t.slots) CUDA_TRY(cudaEventSynchronize(r.s->slots[r.slot].done));
-    float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, t.k0, t.k1) == cudaSuccess) c->stats.last_kernel_ms = ms;
-    for (auto &r : t.slots) {
-        std::lock_guard<std::mutex> sl_lk(r.s->mu);
-        r.s->slots[r.slot].state = SLOT_READY;
-        r.s->newest = r.slot;
-        r.s->n_ready++;
-    }
-    t.slots.clear();
-    t.active = false;
-    c->tick_head = (c->tick_head + 1) % VEP_MAX_TICKS_IN_FLIGHT;
-    c->ticks_in_flight--;
-    return VEP_OK;
+    return retire_ticks(c, 0, true);
+}
+extern "C" int vep_tick_wait_ticket(vep_ctx *c, uint64_t ticket) {
+    if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
+    return retire_ticks(c, ticket, false);
 }
 
 extern "C" int vep_tick(vep_ctx *c, int *n_frames) {
-    int rc = vep_tick_begin(c, n_frames);
+    uint64_t ticket = 0;
+    int rc = vep_tick_begin_ticket(c, n_frames, &ticket);
     if (rc) return rc;
-    return vep_tick_wait(c);
+    return vep_tick_wait_ticket(c, ticket);   // waits for the tick it began (and any older one), whoever else ticks
 }
 
 static int ready_slot(vep_ctx *c, int stream_id, int age, Stream **so, Slot **slo) {
@@ -925,12 +1054,23 @@ extern "C" int vep_result_packed(vep_ctx *c, int stream_id, const uint8_t **msg,
     return vep_result_packed_at(c, stream_id, 0, msg, len);
 }
 
-extern "C" int vep_result_device(vep_ctx *c, int stream_id, const uint8_t **bgr_dev, int32_t shape[3]) {
+extern "C" int vep_result_device_pitched(vep_ctx *c, int stream_id, const uint8_t **bgr_dev, int32_t shape[3], int32_t *row_pitch) {
     Stream *s = nullptr; Slot *sl = nullptr;
     int rc = ready_slot(c, stream_id, 0, &s, &sl);
     if (rc) return rc;
     if (bgr_dev) *bgr_dev = sl->d_out;
     if (shape) { shape[0] = s->h; shape[1] = s->w; shape[2] = 3; }
+    if (row_pitch) *row_pitch = s->pitch_out;
+    return VEP_OK;
+}
+extern "C" int vep_result_device(vep_ctx *c, int stream_id, const uint8_t **bgr_dev, int32_t shape[3]) {
+    int32_t pitch = 0, shp[3] = {0, 0, 0};
+    int rc = vep_result_device_pitched(c, stream_id, bgr_dev, shp, &pitch);
+    if (rc) return rc;
+    if (pitch != 3 * shp[1])
+        return fail(VEP_ERR_GEOMETRY, "stream %d: device rows are padded to %d bytes (width*3 = %d is not a multiple of 16); use vep_result_device_pitched",
+                    stream_id, pitch, 3 * shp[1]);
+    if (shape) { shape[0] = shp[0]; shape[1] = shp[1]; shape[2] = shp[2]; }
     return VEP_OK;
 }
 
@@ -961,13 +1101,17 @@ static constexpr size_t kNoallocWorkOffset = (kNoallocFramesBytes + 255) / 256 *
 static constexpr size_t kNoallocScratchBytes = kNoallocWorkOffset + (size_t)VEP_NOALLOC_MAX_CTAS * sizeof(CtaWork);
 
 // Device-resident scratch: one copy per GPU that loads this library, held until the process exits
-// (about 532 KB).  In HOST code this name is only a handle for cudaGetSymbolAddress — it is not a
+// (545,024 bytes).  In HOST code this name is only a handle for cudaGetSymbolAddress — it is not a
 // device address and must never be handed to a kernel or a memcpy as one.
 static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoallocScratchBytes];
 
 static std::mutex g_noalloc_mu;
 static void *g_noalloc_dev_ptr[64] = {};          // per device ordinal: address of g_noalloc_scratch on that GPU
-static FrameDev g_noalloc_h_frames[VEP_NOALLOC_MAX_FRAMES + 1];   // fixed host staging (no heap use on this path)
+// Fixed host staging (no heap use on this path).  These two arrays are PAGEABLE on purpose: cudaMemcpyAsync from
+// pageable memory returns only after the runtime has taken its own copy of the source (for larger tables it first
+// waits for earlier work on the stream), which is what makes rewriting them on the next call safe.  Do not
+// cudaHostRegister them: from pinned memory the copy would read them later, and an event would have to guard re-use.
+static FrameDev g_noalloc_h_frames[VEP_NOALLOC_MAX_FRAMES + 1];
 static CtaWork g_noalloc_h_work[VEP_NOALLOC_MAX_CTAS];
 
 // Validation + table row for one descriptor; mirrors build_tables() without touching the heap.
@@ -991,7 +1135,7 @@ static int noalloc_frame(const vep_frame_desc &s, int i, FrameDev &f) {
     f.sy = s.stride[0]; f.sc0 = gray ? s.stride[0] : s.stride[1]; f.sc1 = (nv12 || gray) ? 0 : s.stride[2]; f.sd = s.dst_stride;
     f.w = w; f.h = h; f.fmt = s.fmt;
     const size_t ca = nv12 ? 16 : 8;
-    const bool vec = (w % 16 == 0) && aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
+    const bool vec = aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
                      (nv12 || gray || (aligned(f.c1, 8) && f.sc1 % 8 == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
     f.fast = vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;   // the table-driven kernel knows these two paths
     if (vep::fmt_is_422(s.fmt) || vep::fmt_vector_only_when_specialised(s.fmt) || bps == 2) f.fast = vep::PATH_GENERIC;   // ... 4:2:2 / 4:4:4 / gray / 10-bit on the scalar one
@@ -1032,8 +1176,8 @@ extern "C" int vep_convert_batch_noalloc(const vep_frame_desc *descs, int n, voi
         const int per_cta = f.fast != vep::PATH_GENERIC ? vep::kWarpsPerCta : vep::kGenericBlocksPerCta;
         const int ctas = (units + per_cta - 1) / per_cta;
         if (nw + ctas > VEP_NOALLOC_MAX_CTAS)
-            return fail(VEP_ERR_INVALID_ARG, "batch needs more than VEP_NOALLOC_MAX_CTAS (%d) thread blocks (about %d 1080p frames); split the call",
-                        VEP_NOALLOC_MAX_CTAS, VEP_NOALLOC_MAX_CTAS / 270);
+            return fail(VEP_ERR_INVALID_ARG, "batch needs more than VEP_NOALLOC_MAX_CTAS (%d) thread blocks (about %d 1080p frames on the vector path, %d on the scalar one); split the call",
+                        VEP_NOALLOC_MAX_CTAS, VEP_NOALLOC_MAX_CTAS / 270, VEP_NOALLOC_MAX_CTAS / 507);
         for (int k = 0; k < ctas; ++k) g_noalloc_h_work[nw++] = CtaWork{nf, k * per_cta};
         ++nf;
     }
@@ -1044,8 +1188,8 @@ extern "C" int vep_convert_batch_noalloc(const vep_frame_desc *descs, int n, voi
     cudaStream_t st = (cudaStream_t)cuda_stream;
     CUDA_TRY(cudaMemcpyAsync(scratch, g_noalloc_h_frames, (size_t)nf * sizeof(FrameDev), cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(scratch + kNoallocWorkOffset, g_noalloc_h_work, (size_t)nw * sizeof(CtaWork), cudaMemcpyHostToDevice, st));
-    vep::yuv_to_bgr24_batched<0><<<nw, vep::kThreads, 0, st>>>(reinterpret_cast<const FrameDev *>(scratch),
-                                                               reinterpret_cast<const CtaWork *>(scratch + kNoallocWorkOffset));
+    vep::yuv_to_bgr24_batched<<<nw, vep::kThreads, 0, st>>>(reinterpret_cast<const FrameDev *>(scratch),
+                                                            reinterpret_cast<const CtaWork *>(scratch + kNoallocWorkOffset));
     CUDA_TRY(cudaGetLastError());
     return VEP_OK;
 }

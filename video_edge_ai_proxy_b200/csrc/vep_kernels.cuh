@@ -12,10 +12,15 @@
 // per-warp shared-memory tile so that global stores are 16 bytes per lane and contiguous across
 // the warp (3-byte pixels would otherwise scatter 48-byte strided pieces).
 //
-// Three kernels, in file order: yuv_to_bgr24_batched (device tables; fallback beyond 128 frames and
-// the store-mode experiments), yuv_to_bgr24_tick (the DEFAULT: descriptor table in kernel parameters,
-// programmatic dependent launch, per-format instantiations), yuv_to_bgr24_persistent (per-warp TMA
-// pipelines; kept as a measured alternative, slower).  DESIGN.md section 4 has the numbers.
+// Widths that are not a multiple of 16 take the same path when the rows are padded to 16-byte strides: the last
+// lane of a row then loads its 16 bytes partly from the row padding (read, never written) and its partial
+// output chunk leaves as 2-byte stores.
+//
+// Two kernels, in file order: yuv_to_bgr24_batched (descriptor tables in device memory: more than 128 frames
+// per launch, and vep_convert_batch_noalloc) and yuv_to_bgr24_tick (the DEFAULT: descriptor table in kernel
+// parameters, programmatic dependent launch, per-format instantiations).  DESIGN.md section 4 has the numbers,
+// including those of the variants that were measured and removed (TMA bulk-copy persistent kernel, TMA and
+// strided store modes).
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
@@ -30,6 +35,7 @@ constexpr int kThreads = kWarpsPerCta * 32;
 constexpr int kSegPx = 512;                       // pixels per warp item row (32 lanes x 16 px)
 constexpr int kSegBytes = kSegPx * 3;             // 1536 output bytes per row of an item
 constexpr int kGenericBlocksPerCta = 1024;        // 2x2 blocks per CTA on the generic path
+constexpr int kTickRpt = 2;                       // tick kernel: vertically adjacent row pairs per lane (1 measured the same overlapped, 2 % slower in strict order)
 
 enum : int { FMT_YUV420P = 0, FMT_YUVJ420P = 1, FMT_NV12 = 2, FMT_NV21 = 3, FMT_YUV422P = 4, FMT_YUVJ422P = 5, FMT_YUV420P10 = 6, FMT_YUV444P = 7, FMT_YUVJ444P = 8, FMT_GRAY8 = 9 };
 __host__ __device__ constexpr bool fmt_is_semiplanar(int f) { return f == FMT_NV12 || f == FMT_NV21; }
@@ -40,7 +46,7 @@ __host__ __device__ constexpr bool fmt_vector_only_when_specialised(int f) { ret
 __host__ __device__ constexpr bool fmt_is_full_range(int f) { return f == FMT_YUVJ420P || f == FMT_YUVJ422P || f == FMT_YUVJ444P; }
 __host__ __device__ constexpr int fmt_bytes_per_sample(int f) { return f == FMT_YUV420P10 ? 2 : 1; }
 
-enum : int { PATH_GENERIC = 0, PATH_VECTOR = 1, PATH_BULK = 2 };
+enum : int { PATH_GENERIC = 0, PATH_VECTOR = 1 };
 
 struct __align__(16) FrameDev {   // 80 bytes, one per converted frame (+1 sentinel), lives in device memory
     const uint8_t *y, *c0, *c1;   // Y, U|UV, V
@@ -48,12 +54,12 @@ struct __align__(16) FrameDev {   // 80 bytes, one per converted frame (+1 senti
     int32_t sy, sc0, sc1, sd;     // strides in bytes
     int32_t w, h;
     int32_t fmt;
-    int32_t fast;                 // PATH_*: 0 scalar (any even geometry), 1 width%16==0 + vector-aligned,
-                                  //         2 width%32==0 + everything 16-byte aligned (TMA bulk copies)
-    int32_t item_begin;           // first item of this frame in the launch-wide item space (sentinel: total)
+    int32_t fast;                 // PATH_*: 0 scalar (any even geometry, any alignment), 1 vector (16-byte aligned
+                                  //         planes and strides; any even width)
+    int32_t item_begin;           // first work item of this frame in the launch-wide item space (sentinel: total)
     int32_t segs;                 // 512-px segments per row pair
     uint32_t segs_magic;          // ceil(2^32 / segs): rp = umulhi(local, magic) for local < 2^20
-    int32_t fast_tbl;             // PATH_* as seen by the table-driven and persistent kernels (4:2:2 -> generic there)
+    int32_t fast_tbl;             // PATH_* as seen by the table-driven kernel (it has a vector path for 8-bit 4:2:0 only)
 };
 struct CtaWork {                  // 8 bytes per CTA
     int32_t frame;                // index into the FrameDev table
@@ -450,11 +456,28 @@ __device__ __forceinline__ void generic_block(const FrameDev &f, int bx, int by)
     }
 }
 
-// ---- the batched kernel -------------------------------------------------------------------------
-// STORE_MODE 0: shared-memory re-order, then 16 B/lane warp-contiguous st.global
-//            1: shared-memory tile written out by the TMA unit (cp.async.bulk shared -> global)
-//            2: direct 16 B stores from registers (48 B stride between lanes; for comparison)
-template <int STORE_MODE>
+// ---- store of one row segment from the per-warp tile ---------------------------------------------
+// t: the segment's bytes in shared memory (lane l parked its 48 bytes at l*48), g: 16-byte aligned global
+// address of the segment's first byte, seg_bytes: visible bytes (3 * pixels, even).  16 bytes per lane,
+// contiguous across the warp; a last partial chunk (width not a multiple of 16) leaves as 2-byte stores so
+// that nothing beyond the visible pixels is written (swscale overwrites the row padding; we must not).
+__device__ __forceinline__ void store_segment(uint8_t *g, const uint8_t *t, int seg_bytes, int lane) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const int off = (k * 32 + lane) * 16;
+        if (off + 16 <= seg_bytes) {
+            st_stream_v4(g + off, *reinterpret_cast<const uint4 *>(t + off));
+        } else if (off < seg_bytes) {
+            for (int b = off; b < seg_bytes; b += 2)
+                *reinterpret_cast<uint16_t *>(g + b) = *reinterpret_cast<const uint16_t *>(t + b);
+        }
+    }
+}
+
+// ---- the table-driven kernel -----------------------------------------------------------------------
+// Descriptor tables in device memory (FrameDev[], CtaWork[]): the path for more than 128 frames per launch
+// and for vep_convert_batch_noalloc.  One warp item = 512 px x 2 luma rows; shared-memory re-order, then
+// 16 B/lane warp-contiguous st.global.
 __global__ void __launch_bounds__(kThreads)
 yuv_to_bgr24_batched(const FrameDev *__restrict__ frames, const CtaWork *__restrict__ work) {
     __shared__ __align__(128) uint8_t tile[kWarpsPerCta][2][kSegBytes];
@@ -476,26 +499,14 @@ yuv_to_bgr24_batched(const FrameDev *__restrict__ frames, const CtaWork *__restr
     const int x = seg * kSegPx + lane * 16;
 
     uint32_t o0[12], o1[12];
-    const bool active = x < f.w;
+    const bool active = x < f.w;             // the last active lane of a row may cover fewer than 16 visible pixels
     if (active) {
         if (f.fmt == FMT_YUV420P) lane_planar<false>(f, rp, x, o0, o1);
         else if (f.fmt == FMT_YUVJ420P) lane_planar<true>(f, rp, x, o0, o1);
-        else lane_nv12(f, rp, x, o0, o1);   // nv12 / nv21 (4:2:2 frames never reach here: fast_tbl is generic)
+        else lane_nv12(f, rp, x, o0, o1);   // nv12 / nv21 (other formats never reach here: fast_tbl is generic)
     }
     uint8_t *g0 = f.dst + (size_t)(2 * rp) * f.sd + (size_t)seg * kSegBytes;
-    uint8_t *g1 = g0 + f.sd;
-    const int seg_bytes = min(kSegPx, f.w - seg * kSegPx) * 3;   // multiple of 48
-
-    if (STORE_MODE == 2) {
-        if (active) {
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                st_stream_v4(g0 + lane * 48 + k * 16, make_uint4(o0[4 * k], o0[4 * k + 1], o0[4 * k + 2], o0[4 * k + 3]));
-                st_stream_v4(g1 + lane * 48 + k * 16, make_uint4(o1[4 * k], o1[4 * k + 1], o1[4 * k + 2], o1[4 * k + 3]));
-            }
-        }
-        return;
-    }
+    const int seg_bytes = min(kSegPx, f.w - seg * kSegPx) * 3;
 
     uint8_t *t0 = tile[warp][0], *t1 = tile[warp][1];
     if (active) {
@@ -505,29 +516,9 @@ yuv_to_bgr24_batched(const FrameDev *__restrict__ frames, const CtaWork *__restr
             *reinterpret_cast<uint4 *>(t1 + lane * 48 + k * 16) = make_uint4(o1[4 * k], o1[4 * k + 1], o1[4 * k + 2], o1[4 * k + 3]);
         }
     }
-    if (STORE_MODE == 0) {
-        __syncwarp();
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const int off = (k * 32 + lane) * 16;
-            if (off < seg_bytes) {
-                st_stream_v4(g0 + off, *reinterpret_cast<const uint4 *>(t0 + off));
-                st_stream_v4(g1 + off, *reinterpret_cast<const uint4 *>(t1 + off));
-            }
-        }
-    } else {
-        // make the generic-proxy smem writes visible to the async proxy, then one lane hands both
-        // rows to the TMA unit (UBLKCP shared -> global); smem must outlive the read.
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncwarp();
-        if (lane == 0) {
-            const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(t0), s1 = (uint32_t)__cvta_generic_to_shared(t1);
-            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(g0), "r"(s0), "r"(seg_bytes) : "memory");
-            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(g1), "r"(s1), "r"(seg_bytes) : "memory");
-            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-        }
-    }
+    __syncwarp();
+    store_segment(g0, t0, seg_bytes, lane);
+    store_segment(g0 + f.sd, t1, seg_bytes, lane);
 }
 
 
@@ -597,7 +588,7 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     const int rp0 = grp * RPT;
     const int x = seg * kSegPx + lane * 16;
     const bool active = x < f.w;
-    const int seg_bytes = min(kSegPx, f.w - seg * kSegPx) * 3;   // multiple of 48
+    const int seg_bytes = min(kSegPx, f.w - seg * kSegPx) * 3;   // visible bytes of this segment's rows (even)
     uint8_t *t0 = tile[warp][0], *t1 = tile[warp][1];
 
     // ---- all loads first ----
@@ -704,218 +695,10 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
         // writes must be complete before ours land (same output buffer re-used by consecutive launches)
         if (p.wait_prior == 2 && r == 0) asm volatile("griddepcontrol.wait;" ::: "memory");
         uint8_t *g0 = f.dst + (size_t)(2 * rp) * f.sd + (size_t)seg * kSegBytes;
-        uint8_t *g1 = g0 + f.sd;
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const int off = (k * 32 + lane) * 16;
-            if (off < seg_bytes) {
-                st_stream_v4(g0 + off, *reinterpret_cast<const uint4 *>(t0 + off));
-                st_stream_v4(g1 + off, *reinterpret_cast<const uint4 *>(t1 + off));
-            }
-        }
+        store_segment(g0, t0, seg_bytes, lane);
+        store_segment(g0 + f.sd, t1, seg_bytes, lane);
         if (RPT > 1) __syncwarp();                          // tile is re-used by the next row pair
     }
-}
-
-// ================================================================================================
-// Persistent, TMA-pipelined kernel (alternative, VEP_KERNEL=persistent; measured slower than the tick kernel).
-//
-// Item space: every frame contributes items (bulk/vector path: one item = 2 luma rows x 512 px;
-// generic path: one item = 1024 2x2 blocks); FrameDev::item_begin is the running prefix, with a
-// sentinel entry holding the total.  The grid is sized so that every warp gets the same number of
-// items (host: rounds = ceil(items / resident warps); warps = ceil(items / rounds)), and warp w
-// walks items w, w+G, w+2G, ...  Each warp owns a private pipeline in shared memory:
-//
-//   stage[2] (2 KB each)  <- cp.async.bulk global->shared, completion on a per-stage mbarrier,
-//                            issued by lane 0 TWO items ahead, so DRAM latency is off the warp's
-//                            critical path and no lane spends instructions on load addresses
-//   tile (3 KB)           -> lanes park their 2 x 48 output bytes here (conflict-free 48-B stride),
-//                            lane 0 hands both rows to the TMA unit (cp.async.bulk shared->global),
-//                            which writes full 128-B lines; the read of the tile is awaited just
-//                            before the next item's results are parked, one compute phase later
-//
-// No CTA-wide barrier exists; warps of a CTA never wait for one another.
-// ================================================================================================
-constexpr int kPWarps = 4;                 // warps per CTA
-constexpr int kPThreads = kPWarps * 32;
-constexpr int kStages = 2;
-constexpr int kStageBytes = 2048;          // Y0 512 | Y1 512 | planar: U 256, V 256 | nv12: UV 512, UV-above 512
-constexpr int kWarpSmem = kStages * kStageBytes + 2 * kSegBytes + 128;   // + meta/barrier block = 7296
-constexpr int kPSmemBytes = kPWarps * kWarpSmem;
-
-struct StageMeta {        // 32 bytes, written by lane 0 at issue time, read by all lanes at consume time
-    uint8_t *g0;          // first output row of the item
-    int32_t sd;           // output stride
-    int32_t seg_bytes;    // visible bytes per output row of this item (3 * pixels)
-    int32_t flags;        // bits 0-2 fmt, bit 3 nv12/nv21 tail rows, bits 4-5 path
-    int32_t fi;           // frame index
-    int32_t a, b;         // vector path: rp, seg;  generic path: a = first 2x2 block
-};
-
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done = 0;
-    for (int spins = 0; !done; ++spins) {
-        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-        if (!done && spins > (1 << 22)) __trap();   // a lost transaction must fail the launch, not hang the GPU
-    }
-}
-__device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void *src, uint32_t bytes, uint32_t bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(dst_smem), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void bulk_s2g(void *dst, uint32_t src_smem, uint32_t bytes) {
-    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src_smem), "r"(bytes) : "memory");
-}
-
-__global__ void __launch_bounds__(kPThreads)
-yuv_to_bgr24_persistent(const FrameDev *__restrict__ frames, int total_items) {
-    extern __shared__ __align__(128) uint8_t smem_raw[];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    uint8_t *base = smem_raw + warp * kWarpSmem;
-    uint8_t *tile = base + kStages * kStageBytes;
-    StageMeta *meta = reinterpret_cast<StageMeta *>(tile + 2 * kSegBytes);          // 2 x 32 B
-    const uint32_t bar0 = smem_u32(tile + 2 * kSegBytes + 64);                      // 2 x 8 B
-    const uint32_t stage0 = smem_u32(base), tile_s = smem_u32(tile);
-
-    if (lane == 0) {
-        mbar_init(bar0, 1);
-        mbar_init(bar0 + 8, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncwarp();
-
-    const int G = gridDim.x * kPWarps;
-    const int w0 = blockIdx.x * kPWarps + warp;
-    int fi = 0;   // frames are visited in increasing item order: a running index replaces any search
-
-    // ---- issue: decode item -> (frame, row pair, segment), write the stage's meta, start its loads ----
-    auto issue = [&](int item, int s) {
-        if (item >= total_items) return;
-        while (item >= __ldg(&frames[fi + 1].item_begin)) ++fi;
-        const FrameDev *f = frames + fi;
-        const int4 q2 = __ldg(reinterpret_cast<const int4 *>(&f->w));           // w, h, fmt, path
-        const int4 q3 = __ldg(reinterpret_cast<const int4 *>(&f->item_begin));  // item_begin, segs, magic, fast_tbl
-        const int w = q2.x, h = q2.y, fmt = q2.z, path = q3.w;
-        const int local = item - q3.x;
-        if (path == PATH_GENERIC) {
-            if (lane == 0) { meta[s].flags = fmt | (path << 4); meta[s].fi = fi; meta[s].a = local * kGenericBlocksPerCta; }
-            return;
-        }
-        const int segs = q3.y;
-        const int rp = q3.z ? (int)__umulhi((uint32_t)local, (uint32_t)q3.z) : local;   // magic 0 <=> one segment per row
-        const int seg = local - rp * segs;
-        const int wseg = min(kSegPx, w - seg * kSegPx);
-        const int tail = (fmt_is_semiplanar(fmt) && rp == (h >> 1) - 1) ? 1 : 0;
-        if (lane == 0) {
-            const int4 q1 = __ldg(reinterpret_cast<const int4 *>(&f->sy));      // sy, sc0, sc1, sd
-            uint8_t *dst = const_cast<uint8_t *>(reinterpret_cast<const uint8_t *>(__ldg(reinterpret_cast<const unsigned long long *>(&f->dst))));
-            meta[s].g0 = dst + (size_t)(2 * rp) * q1.w + (size_t)seg * kSegBytes;
-            meta[s].sd = q1.w;
-            meta[s].seg_bytes = 3 * wseg;
-            meta[s].flags = fmt | (tail << 3) | (path << 4);
-            meta[s].fi = fi; meta[s].a = rp; meta[s].b = seg;
-            if (path == PATH_BULK) {
-                const uint8_t *y = reinterpret_cast<const uint8_t *>(__ldg(reinterpret_cast<const unsigned long long *>(&f->y)));
-                const uint8_t *c0 = reinterpret_cast<const uint8_t *>(__ldg(reinterpret_cast<const unsigned long long *>(&f->c0)));
-                const uint32_t bar = bar0 + 8 * s, st = stage0 + s * kStageBytes;
-                const uint8_t *yr = y + (size_t)(2 * rp) * q1.x + seg * kSegPx;
-                if (fmt_is_semiplanar(fmt)) {
-                    mbar_expect_tx(bar, 4 * wseg);
-                    bulk_g2s(st, yr, wseg, bar);
-                    bulk_g2s(st + 512, yr + q1.x, wseg, bar);
-                    bulk_g2s(st + 1024, c0 + (size_t)rp * q1.y + seg * kSegPx, wseg, bar);
-                    bulk_g2s(st + 1536, c0 + (size_t)(rp > 0 ? rp - 1 : 0) * q1.y + seg * kSegPx, wseg, bar);
-                } else {
-                    const uint8_t *c1 = reinterpret_cast<const uint8_t *>(__ldg(reinterpret_cast<const unsigned long long *>(&f->c1)));
-                    mbar_expect_tx(bar, 3 * wseg);
-                    bulk_g2s(st, yr, wseg, bar);
-                    bulk_g2s(st + 512, yr + q1.x, wseg, bar);
-                    bulk_g2s(st + 1024, c0 + (size_t)rp * q1.y + seg * (kSegPx / 2), wseg / 2, bar);
-                    bulk_g2s(st + 1280, c1 + (size_t)rp * q1.z + seg * (kSegPx / 2), wseg / 2, bar);
-                }
-            }
-        }
-    };
-
-    issue(w0, 0);
-    issue(w0 + G, 1);
-    __syncwarp();
-    uint32_t phase = 0;   // bit s = parity to wait for on stage s
-
-    int k = 0;
-    for (int item = w0; item < total_items; item += G, ++k) {
-        const int s = k & 1;
-        const StageMeta m = meta[s];            // broadcast read
-        const int fmt = m.flags & 7, path = (m.flags >> 4) & 3;
-        const uint8_t *st = base + s * kStageBytes;
-
-        if (path == PATH_GENERIC) {
-            const FrameDev f = frames[m.fi];
-            const int bw = f.w >> 1, nblk = bw * (f.h >> 1);
-            for (int q = m.a + lane; q < min(m.a + kGenericBlocksPerCta, nblk); q += 32) generic_block(f, q % bw, q / bw);
-            __syncwarp();
-            issue(item + kStages * G, s);
-            __syncwarp();
-            continue;
-        }
-
-        uint32_t o0[12], o1[12];
-        const bool active = lane * 48 < m.seg_bytes;
-        if (path == PATH_BULK) {
-            mbar_wait(bar0 + 8 * s, (phase >> s) & 1);
-            phase ^= 1u << s;
-            if (active) {
-                const uint4 ya = *reinterpret_cast<const uint4 *>(st + lane * 16);
-                const uint4 yb = *reinterpret_cast<const uint4 *>(st + 512 + lane * 16);
-                if (fmt_is_semiplanar(fmt)) {
-                    uint4 cu = *reinterpret_cast<const uint4 *>(st + 1024 + lane * 16);
-                    uint4 pu = *reinterpret_cast<const uint4 *>(st + 1536 + lane * 16);
-                    if (fmt == FMT_NV21) { cu = swap_pairs(cu); pu = swap_pairs(pu); }
-                    compute_nv12(ya, yb, cu, pu, (m.flags >> 3) & 1, o0, o1);
-                } else {
-                    const uint2 uu = *reinterpret_cast<const uint2 *>(st + 1024 + lane * 8);
-                    const uint2 vv = *reinterpret_cast<const uint2 *>(st + 1280 + lane * 8);
-                    if (fmt == FMT_YUV420P) compute_planar<false>(ya, yb, uu, vv, o0, o1);
-                    else compute_planar<true>(ya, yb, uu, vv, o0, o1);
-                }
-            }
-        } else if (active) {   // PATH_VECTOR: per-lane loads straight from global (width % 32 != 0 or 8-byte aligned chroma)
-            const FrameDev f = frames[m.fi];
-            const int x = m.b * kSegPx + lane * 16;
-            if (fmt == FMT_YUV420P) lane_planar<false>(f, m.a, x, o0, o1);
-            else if (fmt == FMT_YUVJ420P) lane_planar<true>(f, m.a, x, o0, o1);
-            else lane_nv12(f, m.a, x, o0, o1);
-        }
-        __syncwarp();                          // every lane has consumed stage s (and its meta)
-        issue(item + kStages * G, s);          // refill it two items ahead
-
-        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // previous item's tile has been read out
-        __syncwarp();
-        if (active) {
-#pragma unroll
-            for (int j = 0; j < 3; ++j) {
-                *reinterpret_cast<uint4 *>(tile + lane * 48 + j * 16) = make_uint4(o0[4 * j], o0[4 * j + 1], o0[4 * j + 2], o0[4 * j + 3]);
-                *reinterpret_cast<uint4 *>(tile + kSegBytes + lane * 48 + j * 16) = make_uint4(o1[4 * j], o1[4 * j + 1], o1[4 * j + 2], o1[4 * j + 3]);
-            }
-        }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the TMA unit
-        __syncwarp();
-        if (lane == 0) {
-            bulk_s2g(m.g0, tile_s, m.seg_bytes);
-            bulk_s2g(m.g0 + m.sd, tile_s + kSegBytes, m.seg_bytes);
-            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-        }
-    }
-    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // all output bytes have left shared memory
 }
 
 }  // namespace vep

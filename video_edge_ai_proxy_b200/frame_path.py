@@ -119,12 +119,19 @@ class Plan:
             pass
 
 
+def launch_sequence(plans: Sequence["Plan"], cuda_stream: int = 0, order: int = _abi.VEP_ORDER_STRICT):
+    """Launch `plans` back to back on one stream from native code (vep_plan_launch_sequence): one ctypes
+    call instead of len(plans), for producers that convert tick after tick."""
+    arr = (C.c_void_p * len(plans))(*[p._h for p in plans])
+    check(_abi.lib().vep_plan_launch_sequence(arr, len(plans), C.c_void_p(cuda_stream), int(order)), "vep_plan_launch_sequence")
+
+
 class _CudaView:
     """Minimal __cuda_array_interface__ carrier so torch can wrap a device pointer without a copy."""
 
-    def __init__(self, ptr: int, shape, owner):
+    def __init__(self, ptr: int, shape, owner, strides=None):
         self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "|u1", "data": (ptr, False),
-                                         "version": 2, "strides": None}
+                                         "version": 2, "strides": strides}
         self._owner = owner
 
 
@@ -224,13 +231,29 @@ class FramePath:
         check(self._L.vep_commit_input(self._ctx, self._sid(device_id),
                                        C.byref(meta) if meta is not None else None), "vep_commit_input")
 
+    def set_staging_threads(self, n: int):
+        """Helper threads that share the staging copy of large (4K) frames with the submitting thread."""
+        check(self._L.vep_set_staging_threads(self._ctx, int(n)), "vep_set_staging_threads")
+
     def tick_begin(self) -> int:
         n = C.c_int()
         check(self._L.vep_tick_begin(self._ctx, C.byref(n)), "vep_tick_begin")
         return n.value
 
     def tick_wait(self):
+        """Wait for the oldest tick in flight."""
         check(self._L.vep_tick_wait(self._ctx), "vep_tick_wait")
+
+    def tick_begin_ticket(self):
+        """(frames in this tick, ticket): the ticket names this tick for tick_wait_ticket (an empty tick
+        returns the ticket of the newest real tick)."""
+        n, t = C.c_int(), C.c_uint64()
+        check(self._L.vep_tick_begin_ticket(self._ctx, C.byref(n), C.byref(t)), "vep_tick_begin_ticket")
+        return n.value, t.value
+
+    def tick_wait_ticket(self, ticket: int):
+        """Return once the tick `ticket` and every older one have landed, whoever else ticks meanwhile."""
+        check(self._L.vep_tick_wait_ticket(self._ctx, C.c_uint64(ticket)), "vep_tick_wait_ticket")
 
     def tick(self) -> int:
         """Convert every staged frame of every camera with one kernel launch; returns the count."""
@@ -255,16 +278,18 @@ class FramePath:
         return memoryview((C.c_uint8 * n.value).from_address(p.value)).cast("B")
 
     def result_tensor(self, device_id: str):
-        """Zero-copy torch CUDA uint8 tensor (H, W, 3) over the device-side result."""
+        """Zero-copy torch CUDA uint8 tensor (H, W, 3) over the device-side result (rows are padded on the
+        device when width*3 is not a multiple of 16: the tensor is then a strided view)."""
         import torch
-        p, shp = C.c_void_p(), (C.c_int32 * 3)()
-        check(self._L.vep_result_device(self._ctx, self._sid(device_id), C.byref(p), shp), "vep_result_device")
-        return torch.as_tensor(_CudaView(p.value, (shp[0], shp[1], shp[2]), self), device=f"cuda:{self.device}")
+        p, shp, pitch = C.c_void_p(), (C.c_int32 * 3)(), C.c_int32()
+        check(self._L.vep_result_device_pitched(self._ctx, self._sid(device_id), C.byref(p), shp, C.byref(pitch)), "vep_result_device_pitched")
+        strides = None if pitch.value == 3 * shp[1] else (pitch.value, 3, 1)
+        return torch.as_tensor(_CudaView(p.value, (shp[0], shp[1], shp[2]), self, strides), device=f"cuda:{self.device}")
 
     # ---- device-resident batches (torch tensors in, torch tensors out) --------------------------
-    def convert_batch(self, descs: Sequence[FrameDesc], cuda_stream: int = 0):
+    def convert_batch(self, descs: Sequence[FrameDesc], cuda_stream: int = 0, order: int = _abi.VEP_ORDER_STRICT):
         arr = (FrameDesc * len(descs))(*descs)
-        check(self._L.vep_convert_batch(self._ctx, arr, len(descs), C.c_void_p(cuda_stream)), "vep_convert_batch")
+        check(self._L.vep_convert_batch_ordered(self._ctx, arr, len(descs), C.c_void_p(cuda_stream), int(order)), "vep_convert_batch_ordered")
 
     def plan(self, descs: Sequence[FrameDesc]) -> Plan:
         return Plan(self, descs)

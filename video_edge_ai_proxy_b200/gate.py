@@ -35,7 +35,13 @@ class DecodeOrder:
 
 
 class DecodeGate:
-    """Per-camera state machine equivalent to the bookkeeping in ReadImage.run."""
+    """Per-camera state machine equivalent to the bookkeeping in ReadImage.run (read_image.py:50-128).
+
+    Protocol per popped packet: `orders = on_packet(...)`; for each order decode that packet of the GOP,
+    call `frame_published()` after every published frame and `packet_done()` once the packet's frames are
+    through.  `packet_done()` is what advances the count of decoded packets — as in the reference, where
+    `packet_count` grows only after a packet went through without an exception (:128), so a packet whose
+    decode or conversion failed is tried again at the next burst instead of being lost."""
 
     def __init__(self):
         self.group_len = 0            # len(packet_group)
@@ -54,12 +60,12 @@ class DecodeGate:
                   and not key_frame_only)
         if self.group_len != 1 and not wanted:
             return []
-        orders = []
-        for gi in range(self.decoded, self.group_len):
-            orders.append(DecodeOrder(gi, self.decoded, self.keyframes, bool(is_keyframe),
-                                      bool(is_corrupt), bool(key_frame_only)))
-            self.decoded += 1
-        return orders
+        return [DecodeOrder(gi, gi, self.keyframes, bool(is_keyframe), bool(is_corrupt), bool(key_frame_only))
+                for gi in range(self.decoded, self.group_len)]
+
+    def packet_done(self):
+        """One ordered packet went through (read_image.py:128)."""
+        self.decoded += 1
 
     def frame_published(self, key_frame_only: bool, query_timestamp: Optional[int]):
         """Call once per published frame (read_image.py:126): remembers the query that was served.

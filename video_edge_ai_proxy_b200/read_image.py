@@ -94,7 +94,8 @@ class ReadImage(threading.Thread):
                 raise ValueError(f"pixel format {fmt!r} is not supported by the B200 frame path")
             if self._opened is not None:
                 self._path.close_stream(self.device_id)     # the camera changed resolution/format mid-stream
-            self._path.open_stream(self.device_id, fmt, w, h, max(int(self._memory_buffer), 1))
+            # the library keeps at most 64 frames readable per camera; Redis MAXLEN holds the history beyond that
+            self._path.open_stream(self.device_id, fmt, w, h, min(max(int(self._memory_buffer), 1), 64))
             self._opened = (fmt, w, h)
 
     def process_packet(self, packet):
@@ -122,6 +123,7 @@ class ReadImage(threading.Thread):
                 if decode_only_keyframes:
                     break
                 self._gate.frame_published(decode_only_keyframes, query_timestamp)
+            self._gate.packet_done()          # counted only once it went through (read_image.py:128)
 
     def run(self):
         while not self._stop_flag.is_set():
