@@ -8,9 +8,15 @@ own 16 cameras on its own GPU (weak scaling, no data-path collective); times are
 
 One JSON line on rank 0:
   value        frames/s with the decoded planes already resident in HBM (kernel-only, CUDA events on
-               the launching stream, K steps back to back, inputs rotate over buffer sets > L2)
+               the launching stream, K steps issued back to back by ONE native call, inputs rotate over
+               buffer sets > L2)
   e2e          frames/s through the public API with HOST buffers: FramePath.submit (pinned staging) ->
-               tick (H2D, kernel, D2H) -> result_packed, copies inside the timed region
+               tick (H2D, kernel, D2H) -> result_packed, copies inside the timed region; beside it the
+               box's DMA ceiling for the same byte mix, probed in the same run on all ranks at once
+               (pinned H2D + D2H only, no kernel, no staging copy), and e2e as a fraction of it
+  parity       before anything is timed: every camera's output of buffer set 0 and every message of the
+               first end-to-end tick are compared byte for byte with the live libswscale; all other
+               buffer sets must equal set 0 exactly.  A mismatch aborts the run.
   roofline     algorithmic bytes (4.5 B/px) per launch / measured launch duration vs MEASURED_PEAKS.json; the headline
                launches consecutive ticks with VEP_ORDER_NONE (disjoint buffer sets); the same K ticks with only the
                stores ordered (`ordered_writes`) and in full stream order (`strict_stream_order`) are reported beside it
@@ -22,11 +28,13 @@ from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import statistics
 import sys
 import threading
 import time
+from collections import deque
 from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
@@ -50,9 +58,12 @@ WORKLOADS = {
     "mixed128-skip": (128, "yuv420p", 0, 0, "128-camera fleet per GPU: 43 x 640x480, 43 x 1280x720, 42 x 1920x1080 yuv420p, interval-skip: each camera converts a frame with p = 0.25 per tick (seeded Bernoulli, seed = tick) (BASELINE configs[4])"),
     "16x1080p-yuvj422p": (16, "yuvj422p", 1920, 1080, "16 synthetic 1080p yuvj422p (MJPEG) cameras per GPU; 5 B/px"),
     "16x1080p-yuv420p10le": (16, "yuv420p10le", 1920, 1080, "16 synthetic 1080p 10-bit 4:2:0 cameras per GPU; 6 B/px"),
-    "16x1080p-yuv444p": (16, "yuv444p", 1920, 1080, "16 synthetic 1080p 4:4:4 cameras per GPU (scalar kernel path); 6 B/px"),
+    "16x1080p-yuv444p": (16, "yuv444p", 1920, 1080, "16 synthetic 1080p 4:4:4 cameras per GPU; 6 B/px"),
     "64x1080p": (64, "yuv420p", 1920, 1080, "64 synthetic 1080p yuv420p cameras on one GPU (launch-overhead study, not a BASELINE config)"),
     "1x480p": (1, "yuv420p", 640, 480, "one 640x480 yuv420p stream (BASELINE configs[0])"),
+    "16x854x480": (16, "yuv420p", 854, 480, "16 synthetic 854x480 yuv420p cameras per GPU: width not a multiple of 16 (rows padded to 16-byte strides, partial last lane)"),
+    "16x1366x768": (16, "yuv420p", 1366, 768, "16 synthetic 1366x768 yuv420p cameras per GPU: width not a multiple of 16 (rows padded to 16-byte strides, partial last lane)"),
+    "16x854x480-tight": (16, "yuv420p", 854, 480, "16 synthetic 854x480 yuv420p cameras per GPU in TIGHT device buffers (stride = width): the scalar kernel path"),
 }
 MIXED_SIZES = [(640, 480)] * 43 + [(1280, 720)] * 43 + [(1920, 1080)] * 42
 
@@ -83,6 +94,18 @@ def schedule_for(workload: str, n_cams: int):
     return [list(range(n_cams))]
 
 
+def config_for(workload: str, steps: int):
+    """The `config` object of the JSON line — the same for both arms (it names the workload, not the arm)."""
+    n, fmt, w, h, desc = WORKLOADS[workload]
+    sched = schedule_for(workload, n)
+    conv = sum(len(sched[i % len(sched)]) for i in range(steps))
+    return {"workload": f"{workload}: {desc}", "cameras_per_gpu": n, "format": fmt,
+            "converted_frames_per_step_per_gpu": round(conv / max(steps, 1), 3),
+            "parallelism": f"cameras sharded {n}/GPU, no collective",
+            "l2": "b200 arm: inputs and outputs rotate over buffer sets whose footprint is >= 3x the GPU's L2 (at least 9 sets; "
+                  "count in roofline.buffer_sets); reference arm: one buffer set per camera in host memory"}
+
+
 def _reduce(value: float, op, device: str):
     import torch
     import torch.distributed as dist
@@ -107,6 +130,31 @@ def barrier():
     import torch.distributed as dist
     if dist.is_available() and dist.is_initialized():
         dist.barrier()
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def pin_rank_cores(local_rank: int, world: int):
+    """Give this rank its own, disjoint share of the host cores (one host process per GPU with its
+    own cores): producer threads, the ticker, the CUDA and NCCL helper threads of a rank then never migrate onto
+    another rank's cores.  Threads started later inherit the mask.  Returns the core list (None: left alone)."""
+    if world <= 1 or os.environ.get("VEP_BENCH_NO_AFFINITY"):
+        return None
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+        per = len(cores) // world
+        if per < 1:
+            return None
+        mine = cores[local_rank * per:(local_rank + 1) * per]
+        os.sched_setaffinity(0, mine)
+        return mine
+    except Exception:
+        return None
 
 
 # ------------------------------------------------------------------------------------------------
@@ -190,50 +238,53 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # CPU arm: the reference's own path on host cores (libswscale via the oracle binding)
 # ------------------------------------------------------------------------------------------------
-def cpu_frames_per_sec(cams, steps: int, warmup: int, threads: int, with_tobytes: bool = True, sched=None, fresh_ctx: bool = False):
-    """Each step converts the frames the tick's schedule selects (default: one frame of every camera —
-    the same tick the GPU arm converts), spread over `threads` host threads; ctypes releases the GIL
-    inside sws_scale.  Returns (converted frames per second, seconds)."""
-    from oracle import swscale_live as live   # bench.py's CPU leg is allowed to execute oracle/
-    from video_edge_ai_proxy_b200.synth import make_planes
-    if not live.available():
-        raise RuntimeError("bundled libswscale not found")
-    threads = max(1, min(threads, len(cams)))
-    convs = []
-    for c in cams:
-        cv = live.Converter(c["fmt"], c["w"], c["h"])
-        cv.load(make_planes(c["fmt"], c["w"], c["h"], c["seed"]))
-        convs.append(cv)
+class CpuArm:
+    """One SwsContext + buffers per camera, a thread pool, and `run(steps)`: each step converts the frames the tick's
+    schedule selects (default: one frame of every camera — the same tick the GPU arm converts), spread over the
+    threads; ctypes releases the GIL inside sws_scale."""
 
-    def one(cv):
-        if fresh_ctx:                                # PyAV builds a reformatter (SwsContext) per decoded frame
-            cv.renew_context()
-        cv.scale()                                   # frame.to_ndarray(format='bgr24')  read_image.py:94
-        if with_tobytes:
-            return cv.result().nbytes                # one H*W*3 copy = np.ndarray.tobytes(img)  :97
-        return 0
+    def __init__(self, cams, threads: int, sched=None):
+        from oracle import swscale_live as live   # bench.py's CPU legs are allowed to execute oracle/
+        from video_edge_ai_proxy_b200.synth import make_planes
+        if not live.available():
+            raise RuntimeError("bundled libswscale not found")
+        self.version = live.version()
+        self.threads = max(1, min(threads, len(cams)))
+        self.convs = []
+        for c in cams:
+            cv = live.Converter(c["fmt"], c["w"], c["h"])
+            cv.load(make_planes(c["fmt"], c["w"], c["h"], c["seed"]))
+            self.convs.append(cv)
+        self.sched = sched or [list(range(len(cams)))]
+        self.pool = ThreadPoolExecutor(self.threads)
 
-    sched = sched or [list(range(len(cams)))]
-    done = 0
-    with ThreadPoolExecutor(threads) as pool:
+    def run(self, steps: int, warmup: int = 0, with_tobytes: bool = True, fresh_ctx: bool = False, threads: int = 0):
+        def one(cv):
+            if fresh_ctx:                                # PyAV builds a reformatter (SwsContext) per decoded frame
+                cv.renew_context()
+            cv.scale()                                   # frame.to_ndarray(format='bgr24')  read_image.py:94
+            if with_tobytes:
+                return cv.result().nbytes                # one H*W*3 copy = np.ndarray.tobytes(img)  :97
+            return 0
+
+        pool = self.pool if not threads else ThreadPoolExecutor(threads)
+        done = 0
         for i in range(warmup):
-            list(pool.map(one, [convs[c] for c in sched[i % len(sched)]]))
+            list(pool.map(one, [self.convs[c] for c in self.sched[i % len(self.sched)]]))
         t0 = time.perf_counter()
         for i in range(steps):
-            sel = sched[i % len(sched)]
-            list(pool.map(one, [convs[c] for c in sel]))
+            sel = self.sched[i % len(self.sched)]
+            list(pool.map(one, [self.convs[c] for c in sel]))
             done += len(sel)
         dt = time.perf_counter() - t0
-    for cv in convs:
-        cv.close()
-    return done / dt, dt
+        if threads:
+            pool.shutdown()
+        return done / dt, dt
 
-
-def host_threads():
-    try:
-        return len(os.sched_getaffinity(0))
-    except Exception:
-        return os.cpu_count() or 1
+    def close(self):
+        self.pool.shutdown()
+        for cv in self.convs:
+            cv.close()
 
 
 def cpu_model():
@@ -259,16 +310,17 @@ def run_reference(args):
     sched = [[r * n + c for r in range(G) for c in pat] for pat in local]
     T = host_threads()
     try:
-        fps, dt = cpu_frames_per_sec(cams, args.steps, args.warmup, T, with_tobytes=True, sched=sched)
+        arm = CpuArm(cams, T, sched)
+        fps, dt = arm.run(args.steps, args.warmup)
     except Exception as e:
         print(json.dumps({"impl": "reference", "unavailable": str(e)[:200]}))
         return 0
-    used = min(T, len(cams))
+    used = arm.threads
     extra = ""
     try:
         few = max(3, min(args.steps, 40))
-        f1, _ = cpu_frames_per_sec(cams, few, 1, 1, with_tobytes=True, sched=sched)
-        ff, _ = cpu_frames_per_sec(cams, few, 1, T, with_tobytes=True, sched=sched, fresh_ctx=True)
+        f1, _ = arm.run(few, 1, threads=1)
+        ff, _ = arm.run(few, 1, fresh_ctx=True)
         extra = f"; 1 thread: {f1:.0f} frames/s; new SwsContext per frame (as PyAV does): {ff:.0f} frames/s"
     except Exception:
         pass
@@ -276,15 +328,15 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC if (w, h) == (1920, 1080) else "bgr24_frames_per_sec", "value": round(fps, 2), "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 4),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {desc}", "frames_per_step": len(cams),
-                   "cpu": cpu_model(), "note": "host cores only; the reference has no GPU path"},
+        "config": config_for(args.workload, args.steps),
         "cpu_baseline": {"value": round(fps, 2), "unit": UNIT, "cores": used, "kind": "reference",
-                         "sample": f"{args.steps} ticks of the workload ({len(cams)} cameras, {fmt}, frames selected per tick as in the GPU arm): libswscale 9.1.100 sws_scale "
-                                   f"(SWS_BILINEAR, the call PyAV makes for read_image.py:94) + tobytes (:97), "
-                                   f"{used} threads of {T} available{extra}; cpu: {cpu_model()}"},
+                         "sample": f"{args.steps} ticks of the workload ({len(cams)} cameras over {G} GPU share(s), {fmt}, frames selected per tick as in the b200 arm): "
+                                   f"libswscale {arm.version} sws_scale (SWS_BILINEAR, the call PyAV makes for read_image.py:94) + tobytes (:97), "
+                                   f"{used} threads of {T} available{extra}; cpu: {cpu_model()}; host cores only, the reference has no GPU path"},
         "e2e": {"value": round(fps, 2), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    arm.close()
     print(json.dumps(line))
     return 0
 
@@ -312,13 +364,89 @@ def ncu_traffic(kernel: str, workload: str):
         return None
 
 
+def _pitch(row_bytes: int) -> int:
+    """Row pitch of device-resident planes/outputs: tight when that is a multiple of 16 bytes, else padded to 64
+    (the layout the library's own staging uses, csrc/vep_abi.cu pitch_of)."""
+    return row_bytes if row_bytes % 16 == 0 else (row_bytes + 63) // 64 * 64
+
+
+def staged_in_bytes(fmt: str, w: int, h: int) -> int:
+    """Bytes of one staged frame = what one H2D copy of the host pipeline moves (csrc/vep_abi.cu vep_stream_open)."""
+    bps = 2 if fmt == "yuv420p10le" else 1
+    semi, gray, c444, c422 = fmt in ("nv12", "nv21"), fmt == "gray", fmt in ("yuv444p", "yuvj444p"), fmt in ("yuv422p", "yuvj422p")
+    a256 = lambda v: (v + 255) // 256 * 256
+    ysz = _pitch(w * bps) * h
+    if gray:
+        return ysz
+    csz = _pitch((w if (semi or c444) else w // 2) * bps) * (h if (c422 or c444) else h // 2)
+    return a256(ysz) + csz if semi else a256(ysz) + a256(csz) + csz
+
+
+def _resident_frame(torch, dev, cam, host_planes, tight: bool):
+    """Device copies of one camera's planes + its output buffer; returns (descriptor, keep-alive, output view (H, W, 3))."""
+    from video_edge_ai_proxy_b200 import desc_from_device_ptrs
+    w, h, fmt = cam["w"], cam["h"], cam["fmt"]
+    planes, ptrs, strides = [], [], []
+    for p in host_planes:
+        pb = np.ascontiguousarray(p).view(np.uint8).reshape(p.shape[0], -1)
+        pitch = pb.shape[1] if tight else _pitch(pb.shape[1])
+        t = torch.zeros((pb.shape[0], pitch), dtype=torch.uint8, device=dev)
+        t[:, :pb.shape[1]] = torch.from_numpy(pb).to(dev)
+        planes.append(t); ptrs.append(t.data_ptr()); strides.append(pitch)
+    opitch = 3 * w if tight else _pitch(3 * w)
+    out = torch.zeros((h, opitch), dtype=torch.uint8, device=dev)
+    d = desc_from_device_ptrs(fmt, w, h, ptrs, strides, out.data_ptr(), opitch)
+    return d, (planes, out), out[:, :3 * w].unflatten(1, (w, 3)) if opitch != 3 * w else out.view(h, w, 3)
+
+
+def dma_ceiling(torch, dev, in_sizes, out_sizes, world, target_bytes=6e9):
+    """What the box's DMA path can carry for this tick's byte mix: every rank copies, from and to pinned host memory,
+    the same H2D and D2H transfers one end-to-end tick makes (one per frame and direction, both directions at once on
+    two streams), back to back, with no kernel and no CPU copy in between.  All ranks run it together, so at N GPUs it
+    is the ceiling of the whole box (PCIe switches, root complexes, host memory), not N times one link."""
+    if not in_sizes:
+        return None
+    reps = max(4, int(math.ceil(target_bytes / float(sum(in_sizes) + sum(out_sizes)))))
+    h_in = [torch.empty(s, dtype=torch.uint8).pin_memory() for s in in_sizes]
+    h_out = [torch.empty(s, dtype=torch.uint8).pin_memory() for s in out_sizes]
+    d_in = [torch.empty(s, dtype=torch.uint8, device=dev) for s in in_sizes]
+    d_out = [torch.zeros(s, dtype=torch.uint8, device=dev) for s in out_sizes]
+    for t in h_in:
+        t.fill_(7)
+    s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+
+    def run(n):
+        for _ in range(n):
+            with torch.cuda.stream(s_in):
+                for a, b in zip(d_in, h_in):
+                    a.copy_(b, non_blocking=True)
+            with torch.cuda.stream(s_out):
+                for a, b in zip(h_out, d_out):
+                    a.copy_(b, non_blocking=True)
+
+    run(2)
+    torch.cuda.synchronize(dev)
+    barrier()
+    t0 = time.perf_counter()
+    run(reps)
+    torch.cuda.synchronize(dev)
+    dt = time.perf_counter() - t0
+    barrier()
+    dt = max_over_ranks(dt) if world > 1 else dt
+    frames = (sum_over_ranks(len(out_sizes)) if world > 1 else len(out_sizes)) * reps
+    nbytes = (sum_over_ranks(sum(in_sizes) + sum(out_sizes)) if world > 1 else sum(in_sizes) + sum(out_sizes)) * reps
+    return {"frames_per_s": frames / dt, "gbs": nbytes / dt / 1e9, "reps": reps, "seconds": dt}
+
+
 def run_gpu(args):
+    rank, local_rank, world = dist_env()
+    my_cores = pin_rank_cores(local_rank, world)     # before torch starts any thread
     import torch
     import torch.distributed as dist
-    from video_edge_ai_proxy_b200 import FramePath, desc_from_tensors, make_meta
+    from video_edge_ai_proxy_b200 import FramePath, launch_sequence, make_meta, videoframe_framing
+    from video_edge_ai_proxy_b200 import _abi
     from video_edge_ai_proxy_b200.synth import make_planes
 
-    rank, local_rank, world = dist_env()
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the GPU arm has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
@@ -327,248 +455,279 @@ def run_gpu(args):
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
 
     n, fmt, w, h, desc = WORKLOADS[args.workload]
+    tight = args.workload.endswith("-tight")
     cams = cameras_for_rank(args.workload, rank, world)
     sched = schedule_for(args.workload, len(cams))
+    n_pat = len(sched)
     alg = [int(ALG_BYTES_BY_FMT.get(c["fmt"], ALG_BYTES_PER_PX) * c["w"] * c["h"]) for c in cams]
     per_set_bytes = sum(alg)
     l2_bytes = torch.cuda.get_device_properties(dev).L2_cache_size
     n_sets = max(args.sets, 2, -(-3 * l2_bytes // per_set_bytes))   # footprint of the rotation >= 3x L2
-    import math
-    while math.gcd(n_sets, len(sched)) != 1:
+    while math.gcd(n_sets, n_pat) != 1:
         n_sets += 1                                                   # coprime: every pattern meets every buffer set
+    conv_in = lambda first, count: sum(len(sched[i % n_pat]) for i in range(first, first + count))
+    bytes_in = lambda first, count: sum(alg[c] for i in range(first, first + count) for c in sched[i % n_pat])
 
     sampler = ClockSampler(local_rank)
     sampler.start()
     path = FramePath(local_rank)
-
-    # ---- resident inputs: n_sets copies of every camera's planes, separate outputs per set ----------
     host_planes = [make_planes(c["fmt"], c["w"], c["h"], c["seed"]) for c in cams]
-    plans, outs = [], []          # plans[s][p]: buffer set s, tick pattern p (None when the pattern converts nothing)
-    for s in range(n_sets):
-        descs, set_outs = [], []
-        for c, hp in zip(cams, host_planes):
-            planes = [torch.from_numpy(p).to(dev) for p in hp]
-            out = torch.zeros((c["h"], c["w"], 3), dtype=torch.uint8, device=dev)
-            descs.append(desc_from_tensors(c["fmt"], planes, out))
-            set_outs.append((planes, out))
-        row = []
-        for pat in sched:
-            row.append(path.plan([descs[c] for c in pat]) if pat else None)
-        plans.append(row)
-        outs.append(set_outs)
-    stream = torch.cuda.current_stream(dev)
-    sptr = stream.cuda_stream
-    n_pat = len(sched)
-
-    def run_ticks(first, count, overlapped):
-        launches = 0
-        for i in range(first, first + count):
-            pl = plans[i % n_sets][i % n_pat]
-            if pl is not None:
-                pl.launch(sptr, overlapped)
-                launches += 1
-        return launches
-
-    warm = max(args.warmup, 3, n_sets * n_pat)        # every (set, pattern) pair is converted at least once
-    run_ticks(0, warm, False)
-    torch.cuda.synchronize(dev)
-    # every set must hold the same, non-trivial result (same inputs): the kernel really ran everywhere
     touched = sorted({c for pat in sched for c in pat})
-    ref_sum = [int(outs[0][c][1].sum(dtype=torch.int64).item()) for c in touched]
-    for s in range(1, n_sets):
-        got = [int(outs[s][c][1].sum(dtype=torch.int64).item()) for c in touched]
-        if got != ref_sum or min(got) == 0:
-            raise SystemExit(f"bench.py: buffer set {s} disagrees with set 0 — refusing to time a broken kernel")
 
-    conv_in = lambda first, count: sum(len(sched[i % n_pat]) for i in range(first, first + count))
-    bytes_in = lambda first, count: sum(alg[c] for i in range(first, first + count) for c in sched[i % n_pat])
+    # ---- parity authority for this run: the live libswscale on this box (outside every timed region) ----
+    parity = {"checked_frames": 0, "checked_messages": 0, "against": None}
+    want = {}
+    if not args.no_parity:
+        from oracle import swscale_live as live        # the checker, never the thing measured
+        if not live.available():
+            raise SystemExit("bench.py: bundled libswscale not found — cannot run the parity gate (use --no-parity to time anyway)")
+        parity["against"] = f"libswscale {live.version()} (sws_scale, SWS_BILINEAR: the call PyAV makes at read_image.py:94), x86 SIMD path"
+        for c in touched:
+            want[c] = live.to_bgr24(cams[c]["fmt"], host_planes[c], cams[c]["w"], cams[c]["h"])
 
-    # ---- value: K steps, device-timed on the launching stream ---------------------------------------
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    torch.cuda.synchronize(dev)
-    w0 = time.perf_counter()
-    e0.record(stream)
-    overlapped = not args.strict_order     # consecutive ticks use disjoint buffer sets -> may overlap
-    gpu_launches = run_ticks(warm, args.steps, overlapped)
-    e1.record(stream)
-    torch.cuda.synchronize(dev)
-    w1 = time.perf_counter()
-    barrier()
-    dev_ms = e0.elapsed_time(e1)
-    dev_ms = max_over_ranks(dev_ms) if world > 1 else dev_ms
-    converted = conv_in(warm, args.steps)
-    total_frames = sum_over_ranks(converted) if world > 1 else converted          # whole job, K steps
-    offered_frames = (sum_over_ranks(len(cams)) if world > 1 else len(cams)) * args.steps
-    value = total_frames / (dev_ms / 1e3)
-    launch_ms = dev_ms / args.steps
-    timed_bytes = bytes_in(warm, args.steps)
-    achieved = timed_bytes / (dev_ms / 1e3) / 1e9      # this rank's GPU (all ranks run the same schedule)
+    line = {"metric": METRIC if (w, h) == (1920, 1080) else "bgr24_frames_per_sec", "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": config_for(args.workload, args.steps)}
+    windows = []
     peak, peak_src = measured_peak()
 
-    # the same K ticks with every launch fully ordered after the previous one (what vep_plan_launch /
-    # vep_convert_batch do by default); reported beside the headline, not instead of it
-    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    torch.cuda.synchronize(dev)
-    s0.record(stream)
-    run_ticks(warm, args.steps, False)
-    s1.record(stream)
-    torch.cuda.synchronize(dev)
-    strict_ms = s0.elapsed_time(s1)
-    strict_ms = max_over_ranks(strict_ms) if world > 1 else strict_ms
-    strict_gbs = timed_bytes / (strict_ms / 1e3) / 1e9
-    # and with only the stores ordered after the previous tick (VEP_ORDER_WRITES: inputs do not come from the previous kernel)
-    o0, o1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize(dev)
-    o0.record(stream)
-    for i in range(warm, warm + args.steps):
-        pl = plans[i % n_sets][i % n_pat]
-        if pl is not None:
-            pl.launch(sptr, order=1)
-    o1.record(stream)
-    torch.cuda.synchronize(dev)
-    ow_ms = o0.elapsed_time(o1)
-    ow_ms = max_over_ranks(ow_ms) if world > 1 else ow_ms
-    ow_gbs = timed_bytes / (ow_ms / 1e3) / 1e9
+    if not args.e2e_only:
+        # ---- resident inputs: n_sets copies of every camera's planes, separate outputs per set ----------
+        plans, outs = [], []          # plans[s][p]: buffer set s, tick pattern p (None when the pattern converts nothing)
+        for s in range(n_sets):
+            descs, set_outs = [], []
+            for c, hp in zip(cams, host_planes):
+                d, keep, view = _resident_frame(torch, dev, c, hp, tight)
+                descs.append(d)
+                set_outs.append((keep, view))
+            plans.append([path.plan([descs[c] for c in pat]) if pat else None for pat in sched])
+            outs.append(set_outs)
+        stream = torch.cuda.current_stream(dev)
+        sptr = stream.cuda_stream
 
-    for row in plans:
-        for p in row:
-            if p is not None:
-                p.close()
-    plans = []
-    del outs, plans
-    torch.cuda.empty_cache()
+        def tick_plans(first, count):
+            return [pl for pl in (plans[i % n_sets][i % n_pat] for i in range(first, first + count)) if pl is not None]
+
+        warm = max(args.warmup, 3, n_sets * n_pat)        # every (set, pattern) pair is converted at least once
+        launch_sequence(tick_plans(0, warm), sptr, _abi.VEP_ORDER_STRICT)
+        torch.cuda.synchronize(dev)
+        # parity gate: set 0 against the live library, every other set against set 0 (same inputs), byte for byte
+        for c in touched:
+            got0 = outs[0][c][1]
+            if want:
+                if not np.array_equal(got0.cpu().numpy(), want[c]):
+                    raise SystemExit(f"bench.py: camera {c} differs from the live libswscale — refusing to time a wrong kernel")
+                parity["checked_frames"] += 1
+            for s in range(1, n_sets):
+                if not torch.equal(outs[s][c][1], got0) or not bool(got0.any()):
+                    raise SystemExit(f"bench.py: buffer set {s} camera {c} disagrees with set 0 — refusing to time a broken kernel")
+        parity["buffer_sets_equal_to_checked_set"] = n_sets - 1
+
+        def timed(order):
+            seq = tick_plans(warm, args.steps)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            torch.cuda.synchronize(dev)
+            t0 = time.perf_counter()
+            e0.record(stream)
+            launch_sequence(seq, sptr, order)          # K launches issued by one native call
+            e1.record(stream)
+            torch.cuda.synchronize(dev)
+            t1 = time.perf_counter()
+            barrier()
+            ms = e0.elapsed_time(e1)
+            return (max_over_ranks(ms) if world > 1 else ms), len(seq), (t0, t1)
+
+        # ---- value: K steps, device-timed on the launching stream; consecutive ticks use disjoint buffer sets ----
+        head_order = _abi.VEP_ORDER_STRICT if args.strict_order else _abi.VEP_ORDER_NONE
+        dev_ms, gpu_launches, win = timed(head_order)
+        windows.append(win)
+        converted = conv_in(warm, args.steps)
+        total_frames = sum_over_ranks(converted) if world > 1 else converted          # whole job, K steps
+        offered_frames = (sum_over_ranks(len(cams)) if world > 1 else len(cams)) * args.steps
+        value = total_frames / (dev_ms / 1e3)
+        timed_bytes = bytes_in(warm, args.steps)
+        achieved = timed_bytes / (dev_ms / 1e3) / 1e9      # this rank's GPU (all ranks run the same schedule)
+        # the same K ticks in full stream order (what vep_plan_launch / vep_convert_batch do by default) and with only the
+        # stores ordered after the previous tick (VEP_ORDER_WRITES); reported beside the headline, not instead of it
+        strict_ms, _, _ = timed(_abi.VEP_ORDER_STRICT)
+        ow_ms, _, _ = timed(_abi.VEP_ORDER_WRITES)
+        strict_gbs, ow_gbs = timed_bytes / (strict_ms / 1e3) / 1e9, timed_bytes / (ow_ms / 1e3) / 1e9
+        written = sum(3 * cams[c]["w"] * cams[c]["h"] for i in range(warm, warm + args.steps) for c in sched[i % n_pat])
+
+        for row in plans:
+            for p in row:
+                if p is not None:
+                    p.close()
+        del outs, plans
+        torch.cuda.empty_cache()
+        kname = "vep::yuv_to_bgr24_tick"
+        line.update({
+            "value": round(value, 1), "ms_per_step": round(dev_ms / args.steps, 5), "gpu_launches": gpu_launches,
+            "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+                         "traffic": ncu_traffic("tick", args.workload),
+                         "traffic_note": "ncu, isolated launch: reads = algorithmic; part of the written bytes is still dirty in the L2 at kernel end and is written back during the next launch",
+                         "peak_source": peak_src, "frac_of_nominal_8TBs": round(achieved / 8000.0, 4),
+                         "alg_bytes_per_launch": int(timed_bytes / max(gpu_launches, 1)), "buffer_sets": n_sets,
+                         "launch": ("strict stream order" if args.strict_order else "VEP_ORDER_NONE: consecutive ticks touch disjoint buffer sets") + "; K launches issued by one vep_plan_launch_sequence call",
+                         "unflushed_write_fraction_upper_bound": round(min(1.0, l2_bytes / max(written, 1)), 4),
+                         "offered_frames_per_s": round(offered_frames / (dev_ms / 1e3), 1),
+                         "strict_stream_order": {"achieved": round(strict_gbs, 1), "frac": round(strict_gbs / peak, 4),
+                                                 "frames_per_s": round(total_frames / (strict_ms / 1e3), 1)},
+                         "ordered_writes": {"achieved": round(ow_gbs, 1), "frac": round(ow_gbs / peak, 4),
+                                            "frames_per_s": round(total_frames / (ow_ms / 1e3), 1)},
+                         "kernel": kname}})
+    else:
+        converted = conv_in(0, args.steps)
 
     # ---- e2e: host planes -> submit -> tick -> packed VideoFrame in pinned memory --------------------
-    e2e_steps = max(3, min(args.steps, args.e2e_steps))
-    names = [f"cam{c['camera']}" for c in cams]
-    for name, c in zip(names, cams):
-        path.open_stream(name, c["fmt"], c["w"], c["h"], memory_buffer=1)
-    meta = make_meta(timestamp=1604660000123, pts=900000, dts=897000, time_base=1 / 90000, is_keyframe=True, frame_type="I", keyframe=1)
-    # one producer thread per camera like the reference, but never more threads than this rank's share of the host
-    pool = ThreadPoolExecutor(max(1, min(len(cams), host_threads() // max(world, 1))))
+    if not args.skip_e2e:
+        e2e_steps = min(max(args.steps, 100), max(args.e2e_steps, 3))
+        names = [f"cam{c['camera']}" for c in cams]
+        for name, c in zip(names, cams):
+            path.open_stream(name, c["fmt"], c["w"], c["h"], memory_buffer=1)
+        meta = make_meta(timestamp=1604660000123, pts=900000, dts=897000, time_base=1 / 90000, is_keyframe=True, frame_type="I", keyframe=1)
+        # one producer thread per camera like the reference, but never more than this rank's share of the host minus the ticker
+        share = len(my_cores) if my_cores else host_threads() // max(world, 1)
+        n_prod = max(1, min(len(cams), share - 1 if share > 1 else 1))
+        pool = ThreadPoolExecutor(n_prod)
+        big = max(int(1.5 * c["w"] * c["h"]) for c in cams) >= (4 << 20)
+        helpers = max(0, min(3, share - 2)) if big else 0
+        path.set_staging_threads(helpers)             # 4K frames: the staging copy of ONE frame is split over helpers + 1 cores
 
-    def stage_async(tick):
-        """Start staging tick `tick`'s frames on the producer threads (one per camera, as in the reference);
-        returns (selected cameras, futures)."""
-        sel = sorted(sched[tick % n_pat])
-        chosen = set(sel)
-        for c in range(len(names)):
-            if c not in chosen:
-                path.submit(names[c], None, None, convert=False)          # gate-skipped: counted, nothing copied
-        return sel, [pool.submit(path.submit, names[c], host_planes[c], meta) for c in sel]
+        def stage_async(tick):
+            """Start staging tick `tick`'s frames on the producer threads; returns (selected cameras, futures)."""
+            sel = sorted(sched[tick % n_pat])
+            chosen = set(sel)
+            for c in range(len(names)):
+                if c not in chosen:
+                    path.submit(names[c], None, None, convert=False)          # gate-skipped: counted, nothing copied
+            return sel, [pool.submit(path.submit, names[c], host_planes[c], meta) for c in sel]
 
-    def join(futs):
-        for f in futs:
-            f.result()
+        def join(futs):
+            for f in futs:
+                f.result()
 
-    def consume(sel):
-        tot = 0
-        for c in sel:
-            tot += len(path.result_packed(names[c]))      # the message a producer hands to XADD
-        return tot
+        def consume(sel):
+            tot = 0
+            for c in sel:
+                tot += len(path.result_packed(names[c]))      # the message a producer hands to XADD
+            return tot
 
-    lat = []
-    for t in range(3 + 30):                           # warm-up, then 30 synchronous ticks for the latency figure
-        sel, futs = stage_async(t); join(futs)
-        l0 = time.perf_counter(); path.tick(); consume(sel)
-        if t >= 3 and sel:
-            lat.append((time.perf_counter() - l0) * 1e3)
-    lat.sort()
-    barrier()
-    torch.cuda.synchronize(dev)
-    base_stats = path.stats()
-    x0 = time.perf_counter()
-    depth, pending, msg_bytes = 3, [], 0              # ticks in flight: H2D of later ticks overlaps D2H of earlier ones
-    sel, futs = stage_async(0)
-    for i in range(e2e_steps):
-        join(futs)                                    # tick i fully staged in pinned memory
-        path.tick_begin()
-        pending.append(sel)
-        if i + 1 < e2e_steps:
-            sel, futs = stage_async(i + 1)            # producers stage the next tick while this thread waits below
-        if len(pending) == depth:
-            path.tick_wait(); msg_bytes = consume(pending.pop(0)) or msg_bytes
-    while pending:
-        path.tick_wait(); msg_bytes = consume(pending.pop(0)) or msg_bytes
-    torch.cuda.synchronize(dev)
-    x1 = time.perf_counter()
-    barrier()
-    st_mid = path.stats()
-    # secondary: the decoder writes its planes straight into the pinned staging slot (vep_acquire_input /
-    # vep_commit_input), so no host copy precedes the H2D.  Every slot already holds a valid frame of its camera.
-    z0 = time.perf_counter()
-    pending = []
-    for i in range(e2e_steps):
-        sel = sorted(sched[i % n_pat])
-        for c in sel:
-            path.acquire_raw(names[c]); path.commit_input(names[c], meta)
-        path.tick_begin(); pending.append(sel)
-        if len(pending) == depth:
-            path.tick_wait(); consume(pending.pop(0))
-    while pending:
-        path.tick_wait(); consume(pending.pop(0))
-    torch.cuda.synchronize(dev)
-    z1 = time.perf_counter()
-    barrier()
-    zc_s = max_over_ranks(z1 - z0) if world > 1 else (z1 - z0)
-    e2e_s = max_over_ranks(x1 - x0) if world > 1 else (x1 - x0)
-    e2e_conv = conv_in(0, e2e_steps)
-    e2e_value = (sum_over_ranks(e2e_conv) if world > 1 else e2e_conv) / e2e_s
-    zc_value = (sum_over_ranks(e2e_conv) if world > 1 else e2e_conv) / zc_s
-    st = st_mid
-    h2d_per_step = (st["h2d_bytes"] - base_stats["h2d_bytes"]) // e2e_steps
-    d2h_per_step = (st["d2h_bytes"] - base_stats["d2h_bytes"]) // e2e_steps
-    pool.shutdown()
+        lat = []
+        checked_cams = set()
+        for t in range(3 + 30):                           # warm-up, then 30 synchronous ticks for the latency figure
+            sel, futs = stage_async(t); join(futs)
+            l0 = time.perf_counter(); path.tick(); consume(sel)
+            if t >= 3 and sel:
+                lat.append((time.perf_counter() - l0) * 1e3)
+            if want and t < n_pat:                        # parity gate, end to end: the first occurrence of every pattern
+                for c in sel:
+                    if c in checked_cams:
+                        continue
+                    pre, suf = videoframe_framing(meta, cams[c]["w"], cams[c]["h"])
+                    if bytes(path.result_packed(names[c])) != pre + want[c].tobytes() + suf:
+                        raise SystemExit(f"bench.py: end-to-end message of camera {c} differs from reference framing + live libswscale pixels")
+                    checked_cams.add(c)
+                    parity["checked_messages"] += 1
+        lat.sort()
+
+        # byte mix of the fullest tick for the ceiling probe: per frame what the library copies in (its staged layout) and out
+        fullest = max(sched, key=len)
+        in_sizes = [staged_in_bytes(cams[c]["fmt"], cams[c]["w"], cams[c]["h"]) for c in fullest]
+        out_sizes = [3 * cams[c]["w"] * cams[c]["h"] for c in fullest]
+        ceiling = dma_ceiling(torch, dev, in_sizes, out_sizes, world) if not args.no_ceiling else None
+
+        barrier()
+        torch.cuda.synchronize(dev)
+        base_stats = path.stats()
+        x0 = time.perf_counter()
+        depth, pending, msg_bytes = 3, deque(), 0         # ticks in flight: H2D of later ticks overlaps D2H of earlier ones
+        sel, futs = stage_async(0)
+        for i in range(e2e_steps):
+            join(futs)                                    # tick i fully staged in pinned memory
+            nconv, ticket = path.tick_begin_ticket()
+            if nconv:
+                pending.append((ticket, sel))
+            if i + 1 < e2e_steps:
+                sel, futs = stage_async(i + 1)            # producers stage the next tick while this thread waits below
+            while len(pending) >= depth:
+                tk, s_ = pending.popleft()
+                path.tick_wait_ticket(tk); msg_bytes = consume(s_) or msg_bytes
+        while pending:
+            tk, s_ = pending.popleft()
+            path.tick_wait_ticket(tk); msg_bytes = consume(s_) or msg_bytes
+        torch.cuda.synchronize(dev)
+        x1 = time.perf_counter()
+        barrier()
+        windows.append((x0, x1))
+        st_mid = path.stats()
+        # secondary: the decoder writes its planes straight into the pinned staging slot (vep_acquire_input /
+        # vep_commit_input), so no host copy precedes the H2D.  Every slot already holds a valid frame of its camera.
+        z0 = time.perf_counter()
+        pending = deque()
+        for i in range(e2e_steps):
+            sel = sorted(sched[i % n_pat])
+            for c in sel:
+                path.acquire_raw(names[c]); path.commit_input(names[c], meta)
+            nconv, ticket = path.tick_begin_ticket()
+            if nconv:
+                pending.append((ticket, sel))
+            while len(pending) >= depth:
+                tk, s_ = pending.popleft()
+                path.tick_wait_ticket(tk); consume(s_)
+        while pending:
+            tk, s_ = pending.popleft()
+            path.tick_wait_ticket(tk); consume(s_)
+        torch.cuda.synchronize(dev)
+        z1 = time.perf_counter()
+        barrier()
+        zc_s = max_over_ranks(z1 - z0) if world > 1 else (z1 - z0)
+        e2e_s = max_over_ranks(x1 - x0) if world > 1 else (x1 - x0)
+        e2e_conv = conv_in(0, e2e_steps)
+        e2e_total = sum_over_ranks(e2e_conv) if world > 1 else e2e_conv
+        e2e_value, zc_value = e2e_total / e2e_s, e2e_total / zc_s
+        h2d_per_step = (st_mid["h2d_bytes"] - base_stats["h2d_bytes"]) // e2e_steps
+        d2h_per_step = (st_mid["d2h_bytes"] - base_stats["d2h_bytes"]) // e2e_steps
+        pcie_job = (sum_over_ranks(h2d_per_step + d2h_per_step) if world > 1 else (h2d_per_step + d2h_per_step)) * e2e_steps / e2e_s / 1e9
+        pool.shutdown()
+        line["e2e"] = {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d_per_step), "d2h_bytes_per_step": int(d2h_per_step),
+                       "steps": e2e_steps,
+                       "api": "FramePath.submit on producer threads (host planes -> pinned staging) + tick_begin_ticket/tick_wait_ticket (3 ticks in flight) + result_packed",
+                       "pcie_gbs": round((h2d_per_step + d2h_per_step) * e2e_steps / e2e_s / 1e9, 2), "pcie_gbs_whole_job": round(pcie_job, 2),
+                       "message_bytes": msg_bytes, "producer_threads": n_prod, "staging_helper_threads": helpers,
+                       "host_cores_of_this_rank": len(my_cores) if my_cores else host_threads(),
+                       "core_pinning": "each rank pinned to its own disjoint share of the host cores" if my_cores else "none (single rank)",
+                       "sync_tick_latency_ms": {"p50": round(lat[len(lat) // 2], 3), "max": round(lat[-1], 3),
+                                                "what": "one tick alone, staged planes -> packed messages readable (H2D + kernel + D2H, no overlap)"} if lat else None,
+                       "decoder_writes_into_pinned_slot": {"value": round(zc_value, 1), "unit": UNIT,
+                                                           "api": "vep_acquire_input/vep_commit_input instead of vep_submit: no host staging copy before the H2D"}}
+        if ceiling:
+            line["e2e"].update({"box_dma_ceiling_gbs": round(ceiling["gbs"], 2), "box_dma_ceiling_frames_per_s": round(ceiling["frames_per_s"], 1),
+                                "frac_of_ceiling": round(e2e_value / ceiling["frames_per_s"], 4),
+                                "decoder_writes_frac_of_ceiling": round(zc_value / ceiling["frames_per_s"], 4),
+                                "ceiling_probe": f"all {world} rank(s) at once: the tick's H2D and D2H transfers from/to pinned memory on two streams, {ceiling['reps']} ticks back to back ({ceiling['seconds']:.2f} s), no kernel, no CPU copy"})
     sampler.stop()
-    clocks = sampler.summary([(w0, w1), (x0, x1)])
+    line["clocks"] = sampler.summary(windows)
+    line["parity"] = parity
     path.close()
 
-    line = {
-        "metric": METRIC if (w, h) == (1920, 1080) else "bgr24_frames_per_sec", "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": round(launch_ms, 5), "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {desc}", "cameras_per_gpu": len(cams), "converted_frames_per_step_per_gpu": round(converted / args.steps, 3),
-                   "offered_frames_per_s": round(offered_frames / (dev_ms / 1e3), 1), "format": fmt,
-                   "l2": f"inputs/outputs rotate over {n_sets} buffer sets of {per_set_bytes / 1e6:.0f} MB (> {l2_bytes / 1e6:.0f} MB L2)",
-                   "parallelism": f"cameras sharded {n}/GPU, no collective", "kernel": os.environ.get("VEP_KERNEL", "tick"),
-                   "launch": "strict stream order" if args.strict_order else "vep_plan_launch_overlapped: consecutive ticks touch disjoint buffer sets"},
-        "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                     "traffic": ncu_traffic(os.environ.get("VEP_KERNEL", "tick"), args.workload),
-                     "traffic_note": "ncu, isolated launch: reads = algorithmic 49.8 MB; ~56 MB of the 99.5 MB written is still dirty in the 126 MB L2 at kernel end and is written back during the next launch",
-                     "peak_source": peak_src, "frac_of_nominal_8TBs": round(achieved / 8000.0, 4),
-                     "alg_bytes_per_launch": int(timed_bytes / max(gpu_launches, 1)),
-                     "strict_stream_order": {"achieved": round(strict_gbs, 1), "frac": round(strict_gbs / peak, 4),
-                                             "frames_per_s": round(total_frames / (strict_ms / 1e3), 1)},
-                     "ordered_writes": {"achieved": round(ow_gbs, 1), "frac": round(ow_gbs / peak, 4),
-                                        "frames_per_s": round(total_frames / (ow_ms / 1e3), 1)}, "kernel": {"persistent": "vep::yuv_to_bgr24_persistent", "oneshot": "vep::yuv_to_bgr24_batched"}.get(os.environ.get("VEP_KERNEL", "tick"), "vep::yuv_to_bgr24_tick")},
-        "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d_per_step), "d2h_bytes_per_step": int(d2h_per_step),
-                "steps": e2e_steps, "api": "FramePath.submit from one producer thread per camera (host planes -> pinned staging) + tick_begin/tick_wait (3 ticks in flight) + result_packed",
-                "pcie_gbs": round((h2d_per_step + d2h_per_step) * e2e_steps / e2e_s / 1e9, 2), "message_bytes": msg_bytes,
-                "producer_threads": pool._max_workers,
-                "sync_tick_latency_ms": {"p50": round(lat[len(lat) // 2], 3), "max": round(lat[-1], 3),
-                                         "what": "one tick alone, staged planes -> packed messages readable (H2D + kernel + D2H, no overlap)"} if lat else None,
-                "decoder_writes_into_pinned_slot": {"value": round(zc_value, 1), "unit": UNIT,
-                                                    "api": "vep_acquire_input/vep_commit_input instead of vep_submit: no host staging copy before the H2D"}},
-        "gpu_launches": gpu_launches,
-        "clocks": clocks,
-    }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         T = host_threads()
         try:
-            # bounded sample: ~20 s of CPU work in total, spread over the host threads
-            frac = converted / max(args.steps * len(cams), 1)                                         # share of frames the gate lets through
-            est_ms = 1.6 * (per_set_bytes / 4.5) / (1920 * 1080) * (1.0 if fmt in ("yuv420p", "yuvj420p") else 5.0) * max(frac, 0.01)
-            cpu_steps = max(3, int(20000 / est_ms))
-            fps, dt = cpu_frames_per_sec(cams, cpu_steps, 2, T, with_tobytes=True, sched=sched if n_pat > 1 else None)
-            fps_scale, _ = cpu_frames_per_sec(cams, max(3, cpu_steps // 4), 1, T, with_tobytes=False, sched=sched if n_pat > 1 else None)
-            fps_one, _ = cpu_frames_per_sec(cams, max(3, cpu_steps // 16), 1, 1, with_tobytes=True, sched=sched if n_pat > 1 else None)
-            used = min(T, len(cams))
-            line["cpu_baseline"] = {"value": round(fps, 1), "unit": UNIT, "cores": used, "kind": "reference",
-                                    "sample": f"{cpu_steps} ticks x {n} frames of the workload ({fmt}, frames selected per tick as in the GPU arm) ({dt:.1f} s wall): libswscale 9.1.100 sws_scale "
-                                              f"(what PyAV calls for read_image.py:94) + tobytes (:97) on {used} threads of {T}; "
+            # bounded sample: time three ticks, then size the sample to ~15 s of wall time on all host threads
+            arm = CpuArm(cams, T, sched if n_pat > 1 else None)
+            _, t3 = arm.run(max(3, n_pat if n_pat <= 30 else 3), 1)
+            per_tick = t3 / max(3, n_pat if n_pat <= 30 else 3)
+            cpu_steps = max(3, min(int(15.0 / max(per_tick, 1e-4)), 20000))
+            fps, dt = arm.run(cpu_steps, 2)
+            fps_scale, _ = arm.run(max(3, cpu_steps // 4), 1, with_tobytes=False)
+            fps_one, _ = arm.run(max(3, cpu_steps // 16), 1, threads=1)
+            line["cpu_baseline"] = {"value": round(fps, 1), "unit": UNIT, "cores": arm.threads, "kind": "reference",
+                                    "sample": f"{cpu_steps} ticks of the workload ({n} cameras, {fmt}, frames selected per tick as in the b200 arm) ({dt:.1f} s wall; sized from three timed ticks): "
+                                              f"libswscale {arm.version} sws_scale (what PyAV calls for read_image.py:94) + tobytes (:97) on {arm.threads} threads of {T}; "
                                               f"sws_scale alone: {fps_scale:.0f} frames/s; 1 thread: {fps_one:.0f} frames/s; cpu: {cpu_model()}"}
+            arm.close()
         except Exception as e:
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {e}"}
     if rank == 0:
@@ -586,8 +745,12 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="16x1080p", choices=sorted(WORKLOADS))
     ap.add_argument("--sets", type=int, default=9, help="minimum number of rotating buffer sets")
-    ap.add_argument("--e2e-steps", type=int, default=300)
+    ap.add_argument("--e2e-steps", type=int, default=300, help="upper bound of end-to-end ticks (at least 100 are run)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the libswscale parity gate (diagnostic runs only)")
+    ap.add_argument("--no-ceiling", action="store_true", help="skip the DMA ceiling probe")
+    ap.add_argument("--e2e-only", action="store_true", help="diagnostic: skip the device-resident legs")
+    ap.add_argument("--skip-e2e", action="store_true", help="diagnostic: skip the end-to-end legs")
     ap.add_argument("--strict-order", action="store_true", help="launch every tick fully ordered after the previous one (no overlap)")
     args = ap.parse_args()
     if args.impl == "reference":
