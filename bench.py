@@ -399,7 +399,7 @@ def _resident_frame(torch, dev, cam, host_planes, tight: bool):
     return d, (planes, out), out[:, :3 * w].unflatten(1, (w, 3)) if opitch != 3 * w else out.view(h, w, 3)
 
 
-def dma_ceiling(torch, dev, in_sizes, out_sizes, world, target_bytes=6e9):
+def dma_ceiling(torch, dev, in_sizes, out_sizes, world, target_bytes=12e9):
     """What the box's DMA path can carry for this tick's byte mix: every rank copies, from and to pinned host memory,
     the same H2D and D2H transfers one end-to-end tick makes (one per frame and direction, both directions at once on
     two streams), back to back, with no kernel and no CPU copy in between.  All ranks run it together, so at N GPUs it
@@ -413,26 +413,31 @@ def dma_ceiling(torch, dev, in_sizes, out_sizes, world, target_bytes=6e9):
     d_out = [torch.zeros(s, dtype=torch.uint8, device=dev) for s in out_sizes]
     for t in h_in:
         t.fill_(7)
-    s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    s_in = [torch.cuda.Stream(dev) for _ in in_sizes]        # one stream per frame and direction, like the pipeline's
+    s_out = [torch.cuda.Stream(dev) for _ in out_sizes]      # per-camera streams
 
     def run(n):
         for _ in range(n):
-            with torch.cuda.stream(s_in):
-                for a, b in zip(d_in, h_in):
+            for st, a, b in zip(s_in, d_in, h_in):
+                with torch.cuda.stream(st):
                     a.copy_(b, non_blocking=True)
-            with torch.cuda.stream(s_out):
-                for a, b in zip(h_out, d_out):
+            for st, a, b in zip(s_out, h_out, d_out):
+                with torch.cuda.stream(st):
                     a.copy_(b, non_blocking=True)
 
     run(2)
     torch.cuda.synchronize(dev)
-    barrier()
-    t0 = time.perf_counter()
-    run(reps)
-    torch.cuda.synchronize(dev)
-    dt = time.perf_counter() - t0
-    barrier()
-    dt = max_over_ranks(dt) if world > 1 else dt
+    best = None
+    for _ in range(3):                                       # a ceiling is a maximum: best of three runs
+        barrier()
+        t0 = time.perf_counter()
+        run(reps)
+        torch.cuda.synchronize(dev)
+        dt = time.perf_counter() - t0
+        barrier()
+        dt = max_over_ranks(dt) if world > 1 else dt
+        best = dt if best is None else min(best, dt)
+    dt = best
     frames = (sum_over_ranks(len(out_sizes)) if world > 1 else len(out_sizes)) * reps
     nbytes = (sum_over_ranks(sum(in_sizes) + sum(out_sizes)) if world > 1 else sum(in_sizes) + sum(out_sizes)) * reps
     return {"frames_per_s": frames / dt, "gbs": nbytes / dt / 1e9, "reps": reps, "seconds": dt}
@@ -526,12 +531,14 @@ def run_gpu(args):
         def timed(order):
             seq = tick_plans(warm, args.steps)
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            # W untimed warm-up steps directly in front of the timed region (the parity checks above left the GPU idle)
+            launch_sequence(tick_plans(warm - max(args.warmup, 3), max(args.warmup, 3)), sptr, order)
+            e0.record(stream); e1.record(stream)        # creates the handles; both are re-recorded below
             barrier()
             torch.cuda.synchronize(dev)
             t0 = time.perf_counter()
-            e0.record(stream)
-            launch_sequence(seq, sptr, order)          # K launches issued by one native call
-            e1.record(stream)
+            # one native call: record e0, K launches, record e1 — on the launching stream, nothing else in between
+            launch_sequence(seq, sptr, order, e0.cuda_event, e1.cuda_event)
             torch.cuda.synchronize(dev)
             t1 = time.perf_counter()
             barrier()
@@ -587,18 +594,30 @@ def run_gpu(args):
         for name, c in zip(names, cams):
             path.open_stream(name, c["fmt"], c["w"], c["h"], memory_buffer=1)
         meta = make_meta(timestamp=1604660000123, pts=900000, dts=897000, time_base=1 / 90000, is_keyframe=True, frame_type="I", keyframe=1)
-        # one producer thread per camera like the reference, but never more than this rank's share of the host minus the ticker
         share = len(my_cores) if my_cores else host_threads() // max(world, 1)
-        n_prod = max(1, min(len(cams), share - 1 if share > 1 else 1))
+        per_camera_threads = args.e2e_submit == "threads"
+        if per_camera_threads:
+            # one producer thread per camera like the reference (each calls vep_submit), never more than this rank's
+            # share of the host minus the ticker; 4K frames: ONE frame's copy is split over a few helper threads
+            n_prod = max(1, min(len(cams), share - 1 if share > 1 else 1))
+            big = max(int(1.5 * c["w"] * c["h"]) for c in cams) >= (4 << 20)
+            helpers = max(0, min(3, share - 2)) if big else 0
+        else:
+            # one producer thread hands the whole tick to the library (vep_submit_batch); the library's helper threads
+            # share the copies (native threads, no interpreter lock between them)
+            n_prod = 1
+            # measured on the 16-core box at N = 1: 1-3 helpers 6.87 k frames/s, 5-7 helpers 6.7 k, none 5.8 k
+            helpers = max(0, min(3, share - 2)) if args.staging_threads < 0 else args.staging_threads
         pool = ThreadPoolExecutor(n_prod)
-        big = max(int(1.5 * c["w"] * c["h"]) for c in cams) >= (4 << 20)
-        helpers = max(0, min(3, share - 2)) if big else 0
-        path.set_staging_threads(helpers)             # 4K frames: the staging copy of ONE frame is split over helpers + 1 cores
+        path.set_staging_threads(helpers)
 
         def stage_async(tick):
-            """Start staging tick `tick`'s frames on the producer threads; returns (selected cameras, futures)."""
+            """Start staging tick `tick`'s frames on the producer thread(s); returns (selected cameras, futures)."""
             sel = sorted(sched[tick % n_pat])
             chosen = set(sel)
+            if not per_camera_threads:
+                items = [(names[c], host_planes[c], meta) if c in chosen else (names[c], None, None) for c in range(len(names))]
+                return sel, [pool.submit(path.submit_many, items)]
             for c in range(len(names)):
                 if c not in chosen:
                     path.submit(names[c], None, None, convert=False)          # gate-skipped: counted, nothing copied
@@ -693,7 +712,8 @@ def run_gpu(args):
         pool.shutdown()
         line["e2e"] = {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d_per_step), "d2h_bytes_per_step": int(d2h_per_step),
                        "steps": e2e_steps,
-                       "api": "FramePath.submit on producer threads (host planes -> pinned staging) + tick_begin_ticket/tick_wait_ticket (3 ticks in flight) + result_packed",
+                       "api": ("FramePath.submit on one producer thread per camera" if per_camera_threads else "FramePath.submit_many: one vep_submit_batch call per tick, copies shared with the library's helper threads")
+                              + " (host planes -> pinned staging) + tick_begin_ticket/tick_wait_ticket (3 ticks in flight) + result_packed",
                        "pcie_gbs": round((h2d_per_step + d2h_per_step) * e2e_steps / e2e_s / 1e9, 2), "pcie_gbs_whole_job": round(pcie_job, 2),
                        "message_bytes": msg_bytes, "producer_threads": n_prod, "staging_helper_threads": helpers,
                        "host_cores_of_this_rank": len(my_cores) if my_cores else host_threads(),
@@ -706,7 +726,7 @@ def run_gpu(args):
             line["e2e"].update({"box_dma_ceiling_gbs": round(ceiling["gbs"], 2), "box_dma_ceiling_frames_per_s": round(ceiling["frames_per_s"], 1),
                                 "frac_of_ceiling": round(e2e_value / ceiling["frames_per_s"], 4),
                                 "decoder_writes_frac_of_ceiling": round(zc_value / ceiling["frames_per_s"], 4),
-                                "ceiling_probe": f"all {world} rank(s) at once: the tick's H2D and D2H transfers from/to pinned memory on two streams, {ceiling['reps']} ticks back to back ({ceiling['seconds']:.2f} s), no kernel, no CPU copy"})
+                                "ceiling_probe": f"all {world} rank(s) at once: the tick's H2D and D2H transfers from/to pinned memory, one stream per frame and direction, {ceiling['reps']} ticks back to back ({ceiling['seconds']:.2f} s, best of 3), no kernel, no CPU copy"})
     sampler.stop()
     line["clocks"] = sampler.summary(windows)
     line["parity"] = parity
@@ -751,6 +771,9 @@ def main():
     ap.add_argument("--no-ceiling", action="store_true", help="skip the DMA ceiling probe")
     ap.add_argument("--e2e-only", action="store_true", help="diagnostic: skip the device-resident legs")
     ap.add_argument("--skip-e2e", action="store_true", help="diagnostic: skip the end-to-end legs")
+    ap.add_argument("--staging-threads", type=int, default=-1, help="library helper threads for the staging copy (default: by this rank's share of the cores)")
+    ap.add_argument("--e2e-submit", default="batch", choices=["batch", "threads"],
+                    help="how host frames reach the library: one vep_submit_batch call per tick (default) or one Python producer thread per camera calling vep_submit")
     ap.add_argument("--strict-order", action="store_true", help="launch every tick fully ordered after the previous one (no overlap)")
     args = ap.parse_args()
     if args.impl == "reference":

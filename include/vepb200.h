@@ -123,8 +123,10 @@ int vep_plan_launch_overlapped(vep_plan *plan, void *cuda_stream);
 #define VEP_ORDER_NONE 2
 int vep_plan_launch_ordered(vep_plan *plan, void *cuda_stream, int order);
 /* plans[0..n) launched back to back on one stream with one call (all of one device): what a native producer
- * converting tick after tick does; saves the per-call overhead of n separate vep_plan_launch_ordered calls. */
-int vep_plan_launch_sequence(vep_plan *const *plans, int n, void *cuda_stream, int order);
+ * converting tick after tick does; saves the per-call overhead of n separate vep_plan_launch_ordered calls.
+ * event_before / event_after: optional cudaEvent_t (NULL: none) recorded on the stream directly before the first
+ * and directly after the last launch, for timing exactly these launches without host latency in between. */
+int vep_plan_launch_sequence(vep_plan *const *plans, int n, void *cuda_stream, int order, void *event_before, void *event_after);
 /* frames with convert!=0, CTAs per launch, algorithmic bytes (read + written: 4.5*W*H per converted 8-bit 4:2:0
  * frame, 5 for 4:2:2, 6 for 4:4:4 and 10-bit, 4 for gray) */
 int vep_plan_info(const vep_plan *plan, int *n_converted, int *n_ctas, int64_t *alg_bytes);
@@ -162,10 +164,10 @@ int vep_convert_batch_noalloc(const vep_frame_desc *descs, int n, void *cuda_str
 int vep_stream_open(vep_ctx *ctx, int stream_id, int fmt, int width, int height, int ring_depth);
 /* Not while ticks are in flight (VEP_ERR_BUSY) and not while another thread is inside a call for this stream. */
 int vep_stream_close(vep_ctx *ctx, int stream_id);
-/* Helper threads for vep_submit's staging copy (default 0).  One core copies 10-16 GB/s into pinned memory, a
- * PCIe Gen5 link takes 55: frames of 4 MB and more (4K) are then cut into row bands copied by the submitting
- * thread and n helpers.  Smaller frames are always copied by the submitting thread alone (one producer thread per
- * camera already covers them, as the reference's one process per camera does). */
+/* Helper threads for the staging copy (default 0).  One core copies 10-16 GB/s into pinned memory, a PCIe Gen5
+ * link takes 55.  vep_submit: frames of 4 MB and more (4K) are cut into pieces copied by the submitting thread and
+ * the helpers; smaller frames are copied by the submitting thread alone (one producer thread per camera already
+ * covers them, as the reference's one process per camera does).  vep_submit_batch: all pieces of all frames. */
 int vep_set_staging_threads(vep_ctx *ctx, int n);
 
 /* Hand one decoded frame (HOST pointers: AVFrame planes + linesizes) to the library.  The planes
@@ -174,6 +176,20 @@ int vep_set_staging_threads(vep_ctx *ctx, int n);
  * different streams; one producer per stream. */
 int vep_submit(vep_ctx *ctx, int stream_id, const uint8_t *const plane[3], const int32_t stride[3],
                const vep_frame_meta *meta, int convert);
+/* The frames of one tick with ONE call (one item per camera, at most one frame per stream and call): the staging
+ * copies of all items are cut into ~1 MB pieces and shared between the calling thread and the context's helper
+ * threads (vep_set_staging_threads), so a producer that gathers many cameras pays one call per tick and the copy
+ * runs on several cores.  Items with convert == 0 are counted like in vep_submit.  Stops at the first item that
+ * cannot be staged (its status is returned, *n_done = items staged and committed before it). */
+typedef struct {
+    int32_t stream_id;
+    int32_t convert;
+    const uint8_t *plane[3];   /* HOST pointers, as for vep_submit */
+    int32_t stride[3];
+    int32_t reserved;
+    vep_frame_meta meta;
+} vep_submit_item;
+int vep_submit_batch(vep_ctx *ctx, const vep_submit_item *items, int n, int *n_done);
 /* Zero-copy variant: get pointers into the next pinned staging slot (a decoder can write its
  * planes there directly), then commit it.  stride_out is the row pitch of each plane in the slot: the row bytes
  * when they are a multiple of 16, else rounded up to 64. */

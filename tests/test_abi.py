@@ -63,6 +63,7 @@ def test_struct_layouts_match_header():
     assert ctypes.sizeof(_abi.FrameMeta) == 64
     assert _abi.FrameDesc.dst.offset == 40 and _abi.FrameDesc.width.offset == 52
     assert _abi.FrameMeta.time_base.offset == 40 and _abi.FrameMeta.frame_type.offset == 56
+    assert ctypes.sizeof(_abi.SubmitItem) == 112 and _abi.SubmitItem.plane.offset == 8 and _abi.SubmitItem.meta.offset == 48
 
 
 def test_library_carries_sm100a_code_only():

@@ -527,3 +527,40 @@ def test_staging_helper_threads_split_a_4k_frame(path):
     assert np.array_equal(path.result("nv12"), F.to_bgr24("nv12", planes))
     with pytest.raises(VepError):
         path.set_staging_threads(1000)
+
+
+def test_submit_many_stages_a_whole_tick_with_helper_threads(path):
+    """vep_submit_batch: every camera's frame of a tick in one call, copies shared with the helper threads; also
+    gate-skipped items, padded decoder strides, ragged widths, and the error position on a full ring."""
+    cams = [("s%d" % i, fmt, w, h) for i, (fmt, w, h) in enumerate(
+        [("yuv420p", 1920, 1080)] * 3 + [("nv12", 3840, 2160), ("yuv420p", 854, 480), ("yuvj422p", 640, 480), ("gray", 50, 6), ("yuv420p10le", 640, 480)])]
+    for name, fmt, w, h in cams:
+        path.open_stream(name, fmt, w, h)
+    for helpers in (0, 3):
+        path.set_staging_threads(helpers)
+        frames, want = [], {}
+        for i, (name, fmt, w, h) in enumerate(cams):
+            if i == 1:
+                frames.append((name, None, None))          # the gate skipped this camera's frame
+                continue
+            planes = make_planes(fmt, w, h, 10 * helpers + i)
+            padded = [np.full((p.shape[0], p.shape[1] + 24), 0xEE, p.dtype) for p in planes]      # decoder-style linesize
+            for b, p in zip(padded, planes):
+                b[:, :p.shape[1]] = p
+            frames.append((name, [b[:, :p.shape[1]] for b, p in zip(padded, planes)], make_meta(timestamp=i + 1, packet=i)))
+            want[name] = F.to_bgr24(fmt, planes)
+        off0 = path.stats()["frames_offered"]
+        assert path.submit_many(frames) == len(cams)
+        assert path.stats()["frames_offered"] - off0 == len(cams)
+        assert path.tick() == len(cams) - 1
+        for name, w_ in want.items():
+            assert np.array_equal(path.result(name), w_), (helpers, name)
+    # a stream whose staging ring is full stops the batch there: items before it are staged, the status says why
+    planes = make_planes("yuv420p", 1920, 1080, 1)
+    for _ in range(6):                                       # 7 slots, one holds the newest result (ring_depth 1)
+        path.submit("s0", planes)
+    with pytest.raises(VepError) as e:
+        path.submit_many([("s2", planes, None), ("s0", planes, None), ("s6", make_planes("gray", 50, 6, 0), None)])
+    assert e.value.status == _abi.VEP_ERR_BUSY
+    assert path.tick() == 7                                  # 6 frames of s0 + the one of s2 staged before the failure
+    path.set_staging_threads(0)

@@ -32,6 +32,11 @@ class FrameMeta(C.Structure):
                 ("frame_type", C.c_char * 8)]
 
 
+class SubmitItem(C.Structure):
+    _fields_ = [("stream_id", C.c_int32), ("convert", C.c_int32), ("plane", C.c_void_p * 3), ("stride", C.c_int32 * 3),
+                ("reserved", C.c_int32), ("meta", FrameMeta)]
+
+
 class Stats(C.Structure):
     _fields_ = [("frames_offered", C.c_int64), ("frames_converted", C.c_int64),
                 ("ticks", C.c_int64), ("kernel_launches", C.c_int64),
@@ -59,7 +64,7 @@ SIGNATURES = {
     "vep_plan_launch": (_i, [_p, _p]),
     "vep_plan_launch_overlapped": (_i, [_p, _p]),
     "vep_plan_launch_ordered": (_i, [_p, _p, _i]),
-    "vep_plan_launch_sequence": (_i, [C.POINTER(C.c_void_p), _i, _p, _i]),
+    "vep_plan_launch_sequence": (_i, [C.POINTER(C.c_void_p), _i, _p, _i, _p, _p]),
     "vep_plan_info": (_i, [_p, _ip, _ip, C.POINTER(C.c_int64)]),
     "vep_plan_destroy": (None, [_p]),
     "vep_stream_open": (_i, [_p, _i, _i, _i, _i, _i]),
@@ -67,6 +72,7 @@ SIGNATURES = {
     "vep_set_staging_threads": (_i, [_p, _i]),
     "vep_submit": (_i, [_p, _i, C.POINTER(C.c_void_p * 3), C.POINTER(C.c_int32 * 3),
                         C.POINTER(FrameMeta), _i]),
+    "vep_submit_batch": (_i, [_p, C.POINTER(SubmitItem), _i, _ip]),
     "vep_acquire_input": (_i, [_p, _i, C.POINTER(C.c_void_p * 3), C.POINTER(C.c_int32 * 3)]),
     "vep_commit_input": (_i, [_p, _i, C.POINTER(FrameMeta)]),
     "vep_tick_begin": (_i, [_p, _ip]),

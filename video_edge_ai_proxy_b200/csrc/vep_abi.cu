@@ -11,6 +11,7 @@
 #include <immintrin.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstdarg>
 #include <cstddef>
 #include <cstdio>
@@ -29,6 +30,7 @@
 static_assert(sizeof(vep_frame_desc) == 72 && offsetof(vep_frame_desc, dst) == 40 && offsetof(vep_frame_desc, width) == 52,
               "vep_frame_desc layout is part of the ABI (mirrored in _abi.py)");
 static_assert(sizeof(vep_frame_meta) == 64 && offsetof(vep_frame_meta, frame_type) == 56, "vep_frame_meta layout is part of the ABI");
+static_assert(sizeof(vep_submit_item) == 112 && offsetof(vep_submit_item, plane) == 8 && offsetof(vep_submit_item, meta) == 48, "vep_submit_item layout is part of the ABI");
 static_assert(sizeof(vep::FrameDev) == 80 && offsetof(vep::FrameDev, w) == 48 && offsetof(vep::FrameDev, item_begin) == 64 &&
               sizeof(vep::CtaWork) == 8, "device table layout (the kernels read 16-byte groups of FrameDev)");
 
@@ -524,12 +526,17 @@ extern "C" int vep_plan_launch_ordered(vep_plan *p, void *cuda_stream, int order
 
 // A run of launches issued from native code in one call: what a C producer that converts tick after tick does, and
 // what the benchmark uses so that the Python call overhead per launch stays out of a short timed region.
-extern "C" int vep_plan_launch_sequence(vep_plan *const *plans, int n, void *cuda_stream, int order) {
+extern "C" int vep_plan_launch_sequence(vep_plan *const *plans, int n, void *cuda_stream, int order, void *event_before, void *event_after) {
     if (n < 0 || (n > 0 && !plans)) return fail(VEP_ERR_INVALID_ARG, "plans is null or n < 0");
     if (order < VEP_ORDER_STRICT || order > VEP_ORDER_NONE) return fail(VEP_ERR_INVALID_ARG, "unknown launch order %d", order);
     for (int i = 0; i < n; ++i) if (!plans[i]) return fail(VEP_ERR_INVALID_ARG, "plans[%d] is null", i);
-    if (n == 0) return VEP_OK;
+    if (n == 0) {
+        if (event_before) CUDA_TRY(cudaEventRecord((cudaEvent_t)event_before, (cudaStream_t)cuda_stream));
+        if (event_after) CUDA_TRY(cudaEventRecord((cudaEvent_t)event_after, (cudaStream_t)cuda_stream));
+        return VEP_OK;
+    }
     DeviceGuard g(plans[0]->ctx->device);
+    if (event_before) CUDA_TRY(cudaEventRecord((cudaEvent_t)event_before, (cudaStream_t)cuda_stream));
     for (int i = 0; i < n; ++i) {
         vep_plan *p = plans[i];
         if (p->ctx->device != plans[0]->ctx->device) return fail(VEP_ERR_INVALID_ARG, "plans[%d] belongs to another device", i);
@@ -538,6 +545,7 @@ extern "C" int vep_plan_launch_sequence(vep_plan *const *plans, int n, void *cud
         __atomic_add_fetch(&p->ctx->stats.kernel_launches, 1, __ATOMIC_RELAXED);
         __atomic_add_fetch(&p->ctx->stats.frames_converted, (int64_t)p->n_converted, __ATOMIC_RELAXED);
     }
+    if (event_after) CUDA_TRY(cudaEventRecord((cudaEvent_t)event_after, (cudaStream_t)cuda_stream));
     return VEP_OK;
 }
 
@@ -786,45 +794,41 @@ static void copy_rows(uint8_t *dst, int dstride, const uint8_t *src, int sstride
 }
 
 struct PlaneCopy { uint8_t *dst; int dstride; const uint8_t *src; int sstride, row_bytes, rows; };
+struct CopyJob { PlaneCopy p; int r0, r1; };
 
-// copy up to three planes; large frames are cut into row bands shared with the context's helper threads
-static void stage_planes(vep_ctx *c, const PlaneCopy *pc, int n_planes) {
-    size_t total = 0;
-    for (int i = 0; i < n_planes; ++i) total += (size_t)pc[i].row_bytes * pc[i].rows;
-    const int helpers = c->stage_threads;
-    if (helpers == 0 || total < kBandSplitBytes) {
-        for (int i = 0; i < n_planes; ++i) copy_rows(pc[i].dst, pc[i].dstride, pc[i].src, pc[i].sstride, pc[i].row_bytes, 0, pc[i].rows);
+// Run the copy jobs on the calling thread plus the context's helper threads: every thread takes the next job off a
+// shared counter until none is left.  Returns when all jobs are done.
+static void run_copy_jobs(vep_ctx *c, const std::vector<CopyJob> &jobs) {
+    auto one = [&jobs](int i) { const CopyJob &j = jobs[i]; copy_rows(j.p.dst, j.p.dstride, j.p.src, j.p.sstride, j.p.row_bytes, j.r0, j.r1); };
+    const int n = (int)jobs.size();
+    const int helpers = std::min(c->stage_threads, n - 1);
+    if (helpers <= 0) {
+        for (int i = 0; i < n; ++i) one(i);
         return;
     }
-    const int parts = helpers + 1;
-    struct Join { std::mutex mu; std::condition_variable cv; int left; } join;
-    join.left = helpers;
-    auto band = [pc, n_planes, parts](int k) {
-        for (int i = 0; i < n_planes; ++i) {
-            const int r0 = (int)((int64_t)pc[i].rows * k / parts), r1 = (int)((int64_t)pc[i].rows * (k + 1) / parts);
-            if (r1 > r0) copy_rows(pc[i].dst, pc[i].dstride, pc[i].src, pc[i].sstride, pc[i].row_bytes, r0, r1);
-        }
-    };
-    for (int k = 1; k < parts; ++k)
-        c->pool.post([&join, band, k] {
-            band(k);
-            std::lock_guard<std::mutex> lk(join.mu);
-            if (--join.left == 0) join.cv.notify_one();
+    struct Shared { std::atomic<int> next{0}; std::mutex mu; std::condition_variable cv; int left; } sh;
+    sh.left = helpers;
+    auto drain = [&sh, &one, n] { for (int i; (i = sh.next.fetch_add(1, std::memory_order_relaxed)) < n;) one(i); };
+    for (int k = 0; k < helpers; ++k)
+        c->pool.post([&sh, drain] {
+            drain();
+            std::lock_guard<std::mutex> lk(sh.mu);
+            if (--sh.left == 0) sh.cv.notify_one();
         });
-    band(0);
-    std::unique_lock<std::mutex> lk(join.mu);
-    join.cv.wait(lk, [&join] { return join.left == 0; });
+    drain();
+    std::unique_lock<std::mutex> lk(sh.mu);
+    sh.cv.wait(lk, [&sh] { return sh.left == 0; });
 }
 
-extern "C" int vep_submit(vep_ctx *c, int stream_id, const uint8_t *const plane[3], const int32_t stride[3],
-                          const vep_frame_meta *meta, int convert) {
-    if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
-    Stream *s = find_stream(c, stream_id);
-    if (!s) return fail(VEP_ERR_INVALID_ARG, "stream %d not open", stream_id);
-    if (!convert) {   // gate said no (read_image.py:80): counted, nothing copied
-        __atomic_add_fetch(&c->stats.frames_offered, 1, __ATOMIC_RELAXED);
-        return VEP_OK;
-    }
+// cut the planes of one frame into jobs of about kJobBytes (whole rows)
+static constexpr size_t kJobBytes = (size_t)1 << 20;
+static void add_plane_jobs(std::vector<CopyJob> &jobs, const PlaneCopy &p) {
+    const int rows_per = std::max(1, (int)(kJobBytes / (size_t)std::max(p.row_bytes, 1)));
+    for (int r = 0; r < p.rows; r += rows_per) jobs.push_back(CopyJob{p, r, std::min(p.rows, r + rows_per)});
+}
+
+// validate one frame against its stream and claim its staging slot; fills the plane copies
+static int prepare_submit(vep_ctx *c, Stream *s, const uint8_t *const plane[3], const int32_t stride[3], PlaneCopy pc[3], int *np) {
     const bool semi = vep::fmt_is_semiplanar(s->fmt), gray = s->fmt == VEP_FMT_GRAY8;
     if (!plane || !stride || !plane[0] || (!gray && (!plane[1] || (!semi && !plane[2])))) return fail(VEP_ERR_INVALID_ARG, "null plane");
     const int bps = vep::fmt_bytes_per_sample(s->fmt);
@@ -836,17 +840,70 @@ extern "C" int vep_submit(vep_ctx *c, int stream_id, const uint8_t *const plane[
     {
         std::lock_guard<std::mutex> lk(s->mu);
         const int i = claim_slot(s);
-        if (i < 0) return fail(VEP_ERR_BUSY, "stream %d: no free staging slot (tick more often or raise ring_depth)", stream_id);
+        if (i < 0) return fail(VEP_ERR_BUSY, "stream %d: no free staging slot (tick more often or raise ring_depth)", s->id);
         plane_ptrs(s, s->slots[i].h_in, pl, st);
     }
-    // the copy runs outside the lock: one producer per stream
+    int n = 0;
+    pc[n++] = PlaneCopy{pl[0], st[0], plane[0], stride[0], s->w * bps, s->h};
+    if (!gray) pc[n++] = PlaneCopy{pl[1], st[1], plane[1], stride[1], cw, crows};
+    if (!semi && !gray) pc[n++] = PlaneCopy{pl[2], st[2], plane[2], stride[2], cw, crows};
+    *np = n;
+    return VEP_OK;
+}
+
+extern "C" int vep_submit(vep_ctx *c, int stream_id, const uint8_t *const plane[3], const int32_t stride[3],
+                          const vep_frame_meta *meta, int convert) {
+    if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
+    Stream *s = find_stream(c, stream_id);
+    if (!s) return fail(VEP_ERR_INVALID_ARG, "stream %d not open", stream_id);
+    if (!convert) {   // gate said no (read_image.py:80): counted, nothing copied
+        __atomic_add_fetch(&c->stats.frames_offered, 1, __ATOMIC_RELAXED);
+        return VEP_OK;
+    }
     PlaneCopy pc[3];
     int np = 0;
-    pc[np++] = PlaneCopy{pl[0], st[0], plane[0], stride[0], s->w * bps, s->h};
-    if (!gray) pc[np++] = PlaneCopy{pl[1], st[1], plane[1], stride[1], cw, crows};
-    if (!semi && !gray) pc[np++] = PlaneCopy{pl[2], st[2], plane[2], stride[2], cw, crows};
-    stage_planes(c, pc, np);
+    int rc = prepare_submit(c, s, plane, stride, pc, &np);
+    if (rc) return rc;
+    // the copy runs outside the lock (one producer per stream); a large frame is shared with the helper threads
+    size_t total = 0;
+    for (int i = 0; i < np; ++i) total += (size_t)pc[i].row_bytes * pc[i].rows;
+    if (c->stage_threads == 0 || total < kBandSplitBytes) {
+        for (int i = 0; i < np; ++i) copy_rows(pc[i].dst, pc[i].dstride, pc[i].src, pc[i].sstride, pc[i].row_bytes, 0, pc[i].rows);
+    } else {
+        std::vector<CopyJob> jobs;
+        for (int i = 0; i < np; ++i) add_plane_jobs(jobs, pc[i]);
+        run_copy_jobs(c, jobs);
+    }
     return vep_commit_input(c, stream_id, meta);
+}
+
+// All frames of a tick with one call: the copies of ALL items are cut into ~1 MB jobs and spread over the calling
+// thread and the helper threads, then every item is committed.  Stops at the first item that cannot be staged.
+extern "C" int vep_submit_batch(vep_ctx *c, const vep_submit_item *items, int n, int *n_done) {
+    if (n_done) *n_done = 0;
+    if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
+    if (n < 0 || (n > 0 && !items)) return fail(VEP_ERR_INVALID_ARG, "items is null or n < 0");
+    std::vector<CopyJob> jobs;
+    int ok = 0, rc = VEP_OK;
+    for (; ok < n; ++ok) {
+        const vep_submit_item &it = items[ok];
+        Stream *s = find_stream(c, it.stream_id);
+        if (!s) { rc = fail(VEP_ERR_INVALID_ARG, "item %d: stream %d not open", ok, it.stream_id); break; }
+        if (!it.convert) continue;
+        PlaneCopy pc[3];
+        int np = 0;
+        rc = prepare_submit(c, s, it.plane, it.stride, pc, &np);
+        if (rc) break;
+        for (int i = 0; i < np; ++i) add_plane_jobs(jobs, pc[i]);
+    }
+    run_copy_jobs(c, jobs);
+    for (int i = 0; i < ok; ++i) {
+        if (!items[i].convert) { __atomic_add_fetch(&c->stats.frames_offered, 1, __ATOMIC_RELAXED); continue; }
+        const int rc2 = vep_commit_input(c, items[i].stream_id, &items[i].meta);
+        if (rc2 && !rc) rc = rc2;
+    }
+    if (n_done) *n_done = ok;
+    return rc;
 }
 
 static void write_framing(Stream *s, Slot &sl) {

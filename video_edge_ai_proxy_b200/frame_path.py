@@ -119,11 +119,15 @@ class Plan:
             pass
 
 
-def launch_sequence(plans: Sequence["Plan"], cuda_stream: int = 0, order: int = _abi.VEP_ORDER_STRICT):
+def launch_sequence(plans: Sequence["Plan"], cuda_stream: int = 0, order: int = _abi.VEP_ORDER_STRICT,
+                    event_before: int = 0, event_after: int = 0):
     """Launch `plans` back to back on one stream from native code (vep_plan_launch_sequence): one ctypes
-    call instead of len(plans), for producers that convert tick after tick."""
+    call instead of len(plans), for producers that convert tick after tick.  event_before / event_after are raw
+    cudaEvent_t handles (e.g. torch.cuda.Event(...).cuda_event of an event that has been recorded once) recorded
+    directly around the launches."""
     arr = (C.c_void_p * len(plans))(*[p._h for p in plans])
-    check(_abi.lib().vep_plan_launch_sequence(arr, len(plans), C.c_void_p(cuda_stream), int(order)), "vep_plan_launch_sequence")
+    check(_abi.lib().vep_plan_launch_sequence(arr, len(plans), C.c_void_p(cuda_stream), int(order),
+                                              C.c_void_p(event_before or None), C.c_void_p(event_after or None)), "vep_plan_launch_sequence")
 
 
 class _CudaView:
@@ -203,6 +207,29 @@ class FramePath:
         ptrs, strides = _plane_ptrs(planes)
         check(self._L.vep_submit(self._ctx, sid, C.byref(ptrs), C.byref(strides),
                                  C.byref(meta) if meta is not None else None, 1), "vep_submit")
+
+    def submit_many(self, frames) -> int:
+        """Stage the frames of one tick with ONE call: `frames` is a sequence of (device_id, planes, meta) — at most
+        one per camera — or (device_id, None, None) for a gate-skipped frame.  The copies are shared between this
+        thread and the helper threads of set_staging_threads().  Returns the number of items staged; raises on the
+        first one that could not be."""
+        arr = (_abi.SubmitItem * len(frames))()
+        for it, (device_id, planes, meta) in zip(arr, frames):
+            it.stream_id = self._sid(device_id)
+            if planes is None:
+                it.convert = 0
+                continue
+            it.convert = 1
+            for i, p in enumerate(planes):
+                if p.dtype not in (np.uint8, np.uint16) or p.ndim != 2 or p.strides[1] != p.itemsize:
+                    raise ValueError("planes must be 2-D uint8 (uint16 for 10-bit formats) arrays with contiguous rows")
+                it.plane[i] = p.ctypes.data
+                it.stride[i] = p.strides[0]
+            if meta is not None:
+                it.meta = meta
+        done = C.c_int()
+        check(self._L.vep_submit_batch(self._ctx, arr, len(frames), C.byref(done)), "vep_submit_batch")
+        return done.value
 
     def acquire_input(self, device_id: str):
         """Writable numpy views of the next pinned staging slot (zero-copy submit); follow with
