@@ -370,18 +370,6 @@ def _pitch(row_bytes: int) -> int:
     return row_bytes if row_bytes % 16 == 0 else (row_bytes + 63) // 64 * 64
 
 
-def staged_in_bytes(fmt: str, w: int, h: int) -> int:
-    """Bytes of one staged frame = what one H2D copy of the host pipeline moves (csrc/vep_abi.cu vep_stream_open)."""
-    bps = 2 if fmt == "yuv420p10le" else 1
-    semi, gray, c444, c422 = fmt in ("nv12", "nv21"), fmt == "gray", fmt in ("yuv444p", "yuvj444p"), fmt in ("yuv422p", "yuvj422p")
-    a256 = lambda v: (v + 255) // 256 * 256
-    ysz = _pitch(w * bps) * h
-    if gray:
-        return ysz
-    csz = _pitch((w if (semi or c444) else w // 2) * bps) * (h if (c422 or c444) else h // 2)
-    return a256(ysz) + csz if semi else a256(ysz) + a256(csz) + csz
-
-
 def _resident_frame(torch, dev, cam, host_planes, tight: bool):
     """Device copies of one camera's planes + its output buffer; returns (descriptor, keep-alive, output view (H, W, 3))."""
     from video_edge_ai_proxy_b200 import desc_from_device_ptrs
@@ -587,7 +575,7 @@ def run_gpu(args):
     else:
         converted = conv_in(0, args.steps)
 
-    # ---- e2e: host planes -> submit -> tick -> packed VideoFrame in pinned memory --------------------
+    # ---- e2e: host planes -> submit -> tick (H2D, kernel, D2H) -> packed VideoFrame in pinned memory ------------
     if not args.skip_e2e:
         e2e_steps = min(max(args.steps, 100), max(args.e2e_steps, 3))
         names = [f"cam{c['camera']}" for c in cams]
@@ -595,26 +583,64 @@ def run_gpu(args):
             path.open_stream(name, c["fmt"], c["w"], c["h"], memory_buffer=1)
         meta = make_meta(timestamp=1604660000123, pts=900000, dts=897000, time_base=1 / 90000, is_keyframe=True, frame_type="I", keyframe=1)
         share = len(my_cores) if my_cores else host_threads() // max(world, 1)
+        # The "decoder's buffer pool": one arena per rank that holds every camera's decoded planes, page-locked ONCE at
+        # set-up (vep_host_register, what a get_buffer callback over a registered arena gives a real decoder).  Frames
+        # in it are submitted without a CPU copy (VEP_SUBMIT_PINNED); the pageable originals serve the secondary leg.
+        # Rows have the linesize a decoder gives them (libavcodec pads linesizes to 64 bytes).
+        ls_of = lambda p: (p.shape[1] * p.itemsize + 63) // 64 * 64
+        need = sum(((ls_of(p) * p.shape[0] + 255) // 256) * 256 for hp in host_planes for p in hp)
+        if args.pool == "register":
+            arena = np.empty(need, np.uint8)
+            path.register_host(arena)                     # cudaHostRegister over memory the producer allocated itself
+        else:
+            arena_t = torch.empty(need, dtype=torch.uint8).pin_memory()       # cudaHostAlloc'ed by the producer
+            arena = arena_t.numpy()
+        pinned_planes, off = [], 0
+        for hp in host_planes:
+            views = []
+            for p in hp:
+                ls, rb = ls_of(p), p.shape[1] * p.itemsize
+                rows = arena[off:off + ls * p.shape[0]].reshape(p.shape[0], ls)
+                rows[:, :rb] = p.view(np.uint8).reshape(p.shape[0], rb)
+                views.append(rows[:, :rb].view(p.dtype))
+                off += ((ls * p.shape[0] + 255) // 256) * 256
+            pinned_planes.append(views)
         per_camera_threads = args.e2e_submit == "threads"
         if per_camera_threads:
-            # one producer thread per camera like the reference (each calls vep_submit), never more than this rank's
-            # share of the host minus the ticker; 4K frames: ONE frame's copy is split over a few helper threads
+            # pageable leg, variant: one producer thread per camera like the reference (each calls vep_submit), never more
+            # than this rank's share of the host minus the ticker; 4K frames: ONE frame's copy is split over helper threads
             n_prod = max(1, min(len(cams), share - 1 if share > 1 else 1))
             big = max(int(1.5 * c["w"] * c["h"]) for c in cams) >= (4 << 20)
             helpers = max(0, min(3, share - 2)) if big else 0
         else:
-            # one producer thread hands the whole tick to the library (vep_submit_batch); the library's helper threads
-            # share the copies (native threads, no interpreter lock between them)
+            # pageable leg: one producer thread hands the whole tick to the library (vep_submit_batch); the library's
+            # helper threads share the copies.  Measured on the 16-core box at N = 1: 1-3 helpers 6.87 k frames/s,
+            # 5-7 helpers 6.7 k, none 5.8 k
             n_prod = 1
-            # measured on the 16-core box at N = 1: 1-3 helpers 6.87 k frames/s, 5-7 helpers 6.7 k, none 5.8 k
             helpers = max(0, min(3, share - 2)) if args.staging_threads < 0 else args.staging_threads
         pool = ThreadPoolExecutor(n_prod)
         path.set_staging_threads(helpers)
 
-        def stage_async(tick):
-            """Start staging tick `tick`'s frames on the producer thread(s); returns (selected cameras, futures)."""
+        class _Done:                      # a finished "future" for work done inline
+            def result(self):
+                return None
+
+        def stage_async(tick, pinned):
+            """Stage tick `tick`'s frames; returns (selected cameras, futures to join before tick_begin).
+            pinned: "slot" = the decoder wrote the frame into the library's pinned slot (vep_acquire_input/vep_commit_input),
+            True = the frame lies in the producer's own page-locked pool (VEP_SUBMIT_PINNED), False = pageable (VEP_SUBMIT_COPY)."""
             sel = sorted(sched[tick % n_pat])
             chosen = set(sel)
+            if pinned == "slot":
+                for c in range(len(names)):
+                    if c in chosen:
+                        path.acquire_raw(names[c]); path.commit_input(names[c], meta)
+                    else:
+                        path.submit(names[c], None, None, convert=False)
+                return sel, [_Done()]
+            if pinned:                    # no copy: one cheap native call, made inline by the ticker thread
+                path.submit_many([(names[c], pinned_planes[c], meta) if c in chosen else (names[c], None, None) for c in range(len(names))], pinned=True)
+                return sel, [_Done()]
             if not per_camera_threads:
                 items = [(names[c], host_planes[c], meta) if c in chosen else (names[c], None, None) for c in range(len(names))]
                 return sel, [pool.submit(path.submit_many, items)]
@@ -633,100 +659,106 @@ def run_gpu(args):
                 tot += len(path.result_packed(names[c]))      # the message a producer hands to XADD
             return tot
 
-        lat = []
-        checked_cams = set()
-        for t in range(3 + 30):                           # warm-up, then 30 synchronous ticks for the latency figure
-            sel, futs = stage_async(t); join(futs)
-            l0 = time.perf_counter(); path.tick(); consume(sel)
-            if t >= 3 and sel:
-                lat.append((time.perf_counter() - l0) * 1e3)
-            if want and t < n_pat:                        # parity gate, end to end: the first occurrence of every pattern
-                for c in sel:
-                    if c in checked_cams:
-                        continue
-                    pre, suf = videoframe_framing(meta, cams[c]["w"], cams[c]["h"])
-                    if bytes(path.result_packed(names[c])) != pre + want[c].tobytes() + suf:
-                        raise SystemExit(f"bench.py: end-to-end message of camera {c} differs from reference framing + live libswscale pixels")
-                    checked_cams.add(c)
-                    parity["checked_messages"] += 1
-        lat.sort()
+        def warm_and_check(pinned, ticks, lat=None):
+            """Synchronous ticks: warm-up, latency samples, and the end-to-end parity gate (first occurrence of every pattern)."""
+            checked = set()
+            for t in range(ticks):
+                sel, futs = stage_async(t, pinned); join(futs)
+                l0 = time.perf_counter(); path.tick(); consume(sel)
+                if lat is not None and t >= 3 and sel:
+                    lat.append((time.perf_counter() - l0) * 1e3)
+                if want and t < n_pat:
+                    for c in sel:
+                        if c in checked:
+                            continue
+                        pre, suf = videoframe_framing(meta, cams[c]["w"], cams[c]["h"])
+                        if bytes(path.result_packed(names[c])) != pre + want[c].tobytes() + suf:
+                            raise SystemExit(f"bench.py: end-to-end message of camera {c} (source mode {pinned!r}) differs from reference framing + live libswscale pixels")
+                        checked.add(c)
+                        parity["checked_messages"] += 1
 
-        # byte mix of the fullest tick for the ceiling probe: per frame what the library copies in (its staged layout) and out
+        def timed_e2e(pinned):
+            barrier()
+            torch.cuda.synchronize(dev)
+            s0 = path.stats()
+            x0 = time.perf_counter()
+            depth, pending, msg_bytes = 3, deque(), 0         # ticks in flight: H2D of later ticks overlaps D2H of earlier ones
+            sel, futs = stage_async(0, pinned)
+            for i in range(e2e_steps):
+                join(futs)                                    # tick i fully staged
+                nconv, ticket = path.tick_begin_ticket()
+                if nconv:
+                    pending.append((ticket, sel))
+                if i + 1 < e2e_steps:
+                    sel, futs = stage_async(i + 1, pinned)    # pageable source: the copy runs while this thread waits below
+                while len(pending) >= depth:
+                    tk, s_ = pending.popleft()
+                    path.tick_wait_ticket(tk); msg_bytes = consume(s_) or msg_bytes
+            while pending:
+                tk, s_ = pending.popleft()
+                path.tick_wait_ticket(tk); msg_bytes = consume(s_) or msg_bytes
+            torch.cuda.synchronize(dev)
+            x1 = time.perf_counter()
+            barrier()
+            s1 = path.stats()
+            secs = max_over_ranks(x1 - x0) if world > 1 else (x1 - x0)
+            return secs, (x0, x1), msg_bytes, (s1["h2d_bytes"] - s0["h2d_bytes"]) // e2e_steps, (s1["d2h_bytes"] - s0["d2h_bytes"]) // e2e_steps
+
+        # the decoder's writes into the library's pinned slots: every slot of every camera receives its camera's frame once
+        # (the timed region then re-submits them; decoding itself is outside this path in both arms)
+        for _ in range(8 + 2):                              # ring 1 + 4 in flight + 2 spare slots, and then some
+            for c in range(len(names)):
+                for v, p in zip(path.acquire_input(names[c]), host_planes[c]):
+                    v[...] = p
+                path.commit_input(names[c], meta)
+            path.tick()
+        lat = []
+        warm_and_check("slot", 3 + 30, lat)                # warm-up, then 30 synchronous ticks for the latency figure
+        lat.sort()
+        # byte mix of the fullest tick for the ceiling probe: per frame what the library copies in and out
         fullest = max(sched, key=len)
-        in_sizes = [staged_in_bytes(cams[c]["fmt"], cams[c]["w"], cams[c]["h"]) for c in fullest]
+        in_sizes = [path.staged_bytes(names[c]) for c in fullest]
         out_sizes = [3 * cams[c]["w"] * cams[c]["h"] for c in fullest]
         ceiling = dma_ceiling(torch, dev, in_sizes, out_sizes, world) if not args.no_ceiling else None
 
-        barrier()
-        torch.cuda.synchronize(dev)
-        base_stats = path.stats()
-        x0 = time.perf_counter()
-        depth, pending, msg_bytes = 3, deque(), 0         # ticks in flight: H2D of later ticks overlaps D2H of earlier ones
-        sel, futs = stage_async(0)
-        for i in range(e2e_steps):
-            join(futs)                                    # tick i fully staged in pinned memory
-            nconv, ticket = path.tick_begin_ticket()
-            if nconv:
-                pending.append((ticket, sel))
-            if i + 1 < e2e_steps:
-                sel, futs = stage_async(i + 1)            # producers stage the next tick while this thread waits below
-            while len(pending) >= depth:
-                tk, s_ = pending.popleft()
-                path.tick_wait_ticket(tk); msg_bytes = consume(s_) or msg_bytes
-        while pending:
-            tk, s_ = pending.popleft()
-            path.tick_wait_ticket(tk); msg_bytes = consume(s_) or msg_bytes
-        torch.cuda.synchronize(dev)
-        x1 = time.perf_counter()
-        barrier()
-        windows.append((x0, x1))
-        st_mid = path.stats()
-        # secondary: the decoder writes its planes straight into the pinned staging slot (vep_acquire_input /
-        # vep_commit_input), so no host copy precedes the H2D.  Every slot already holds a valid frame of its camera.
-        z0 = time.perf_counter()
-        pending = deque()
-        for i in range(e2e_steps):
-            sel = sorted(sched[i % n_pat])
-            for c in sel:
-                path.acquire_raw(names[c]); path.commit_input(names[c], meta)
-            nconv, ticket = path.tick_begin_ticket()
-            if nconv:
-                pending.append((ticket, sel))
-            while len(pending) >= depth:
-                tk, s_ = pending.popleft()
-                path.tick_wait_ticket(tk); consume(s_)
-        while pending:
-            tk, s_ = pending.popleft()
-            path.tick_wait_ticket(tk); consume(s_)
-        torch.cuda.synchronize(dev)
-        z1 = time.perf_counter()
-        barrier()
-        zc_s = max_over_ranks(z1 - z0) if world > 1 else (z1 - z0)
-        e2e_s = max_over_ranks(x1 - x0) if world > 1 else (x1 - x0)
+        e2e_s, win, msg_bytes, h2d_per_step, d2h_per_step = timed_e2e("slot")
+        windows.append(win)
+        warm_and_check(False, max(3, min(n_pat, 30)))
+        pg_s, _, _, pg_h2d, _ = timed_e2e(False)
+        warm_and_check(True, max(3, min(n_pat, 30)))
+        pp_s, _, _, pp_h2d, _ = timed_e2e(True)
         e2e_conv = conv_in(0, e2e_steps)
         e2e_total = sum_over_ranks(e2e_conv) if world > 1 else e2e_conv
-        e2e_value, zc_value = e2e_total / e2e_s, e2e_total / zc_s
-        h2d_per_step = (st_mid["h2d_bytes"] - base_stats["h2d_bytes"]) // e2e_steps
-        d2h_per_step = (st_mid["d2h_bytes"] - base_stats["d2h_bytes"]) // e2e_steps
+        e2e_value, pg_value, pp_value = e2e_total / e2e_s, e2e_total / pg_s, e2e_total / pp_s
         pcie_job = (sum_over_ranks(h2d_per_step + d2h_per_step) if world > 1 else (h2d_per_step + d2h_per_step)) * e2e_steps / e2e_s / 1e9
         pool.shutdown()
+        path.set_staging_threads(0)
         line["e2e"] = {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": int(h2d_per_step), "d2h_bytes_per_step": int(d2h_per_step),
                        "steps": e2e_steps,
-                       "api": ("FramePath.submit on one producer thread per camera" if per_camera_threads else "FramePath.submit_many: one vep_submit_batch call per tick, copies shared with the library's helper threads")
-                              + " (host planes -> pinned staging) + tick_begin_ticket/tick_wait_ticket (3 ticks in flight) + result_packed",
+                       "api": "decoded planes written by the decoder into the library's pinned staging slots (vep_acquire_input hands the plane pointers to its get_buffer callback, "
+                              "vep_commit_input submits the frame: no CPU copy) -> tick_begin_ticket/tick_wait_ticket (H2D, one kernel launch, D2H; 3 ticks in flight) -> result_packed",
                        "pcie_gbs": round((h2d_per_step + d2h_per_step) * e2e_steps / e2e_s / 1e9, 2), "pcie_gbs_whole_job": round(pcie_job, 2),
-                       "message_bytes": msg_bytes, "producer_threads": n_prod, "staging_helper_threads": helpers,
+                       "message_bytes": msg_bytes,
                        "host_cores_of_this_rank": len(my_cores) if my_cores else host_threads(),
                        "core_pinning": "each rank pinned to its own disjoint share of the host cores" if my_cores else "none (single rank)",
                        "sync_tick_latency_ms": {"p50": round(lat[len(lat) // 2], 3), "max": round(lat[-1], 3),
-                                                "what": "one tick alone, staged planes -> packed messages readable (H2D + kernel + D2H, no overlap)"} if lat else None,
-                       "decoder_writes_into_pinned_slot": {"value": round(zc_value, 1), "unit": UNIT,
-                                                           "api": "vep_acquire_input/vep_commit_input instead of vep_submit: no host staging copy before the H2D"}}
+                                                "what": "one tick alone, planes in pinned memory -> packed messages readable (H2D + kernel + D2H, no overlap)"} if lat else None,
+                       "pageable_source": {"value": round(pg_value, 1), "unit": UNIT, "h2d_bytes_per_step": int(pg_h2d),
+                                           "api": ("FramePath.submit on one producer thread per camera" if per_camera_threads else "FramePath.submit_many: one vep_submit_batch call per tick on a producer thread, copies shared with the library's helper threads")
+                                                  + " [VEP_SUBMIT_COPY: pageable planes (what PyAV hands out) -> staging copy into pinned slots] -> same tick pipeline",
+                                           "producer_threads": n_prod, "staging_helper_threads": helpers},
+                       "caller_pinned_pool": {"value": round(pp_value, 1), "unit": UNIT, "h2d_bytes_per_step": int(pp_h2d),
+                                              "api": "planes in the producer's OWN page-locked frame pool (decoder linesizes, 64-byte aligned) -> FramePath.submit_many(pinned=True) "
+                                                     "[vep_submit_batch, VEP_SUBMIT_PINNED: no CPU copy, one H2D copy per plane] -> same tick pipeline"}}
         if ceiling:
             line["e2e"].update({"box_dma_ceiling_gbs": round(ceiling["gbs"], 2), "box_dma_ceiling_frames_per_s": round(ceiling["frames_per_s"], 1),
                                 "frac_of_ceiling": round(e2e_value / ceiling["frames_per_s"], 4),
-                                "decoder_writes_frac_of_ceiling": round(zc_value / ceiling["frames_per_s"], 4),
                                 "ceiling_probe": f"all {world} rank(s) at once: the tick's H2D and D2H transfers from/to pinned memory, one stream per frame and direction, {ceiling['reps']} ticks back to back ({ceiling['seconds']:.2f} s, best of 3), no kernel, no CPU copy"})
+            line["e2e"]["pageable_source"]["frac_of_ceiling"] = round(pg_value / ceiling["frames_per_s"], 4)
+            line["e2e"]["caller_pinned_pool"]["frac_of_ceiling"] = round(pp_value / ceiling["frames_per_s"], 4)
+        if args.pool == "register":
+            path.unregister_host(arena)
+        line["e2e"]["caller_pinned_pool"]["frame_pool"] = "cudaHostRegister (vep_host_register) over the producer's own allocation" if args.pool == "register" else "cudaHostAlloc'ed by the producer"
     sampler.stop()
     line["clocks"] = sampler.summary(windows)
     line["parity"] = parity
@@ -772,6 +804,7 @@ def main():
     ap.add_argument("--e2e-only", action="store_true", help="diagnostic: skip the device-resident legs")
     ap.add_argument("--skip-e2e", action="store_true", help="diagnostic: skip the end-to-end legs")
     ap.add_argument("--staging-threads", type=int, default=-1, help="library helper threads for the staging copy (default: by this rank's share of the cores)")
+    ap.add_argument("--pool", default="register", choices=["register", "alloc"], help="how the producer's frame pool of the e2e leg is page-locked")
     ap.add_argument("--e2e-submit", default="batch", choices=["batch", "threads"],
                     help="how host frames reach the library: one vep_submit_batch call per tick (default) or one Python producer thread per camera calling vep_submit")
     ap.add_argument("--strict-order", action="store_true", help="launch every tick fully ordered after the previous one (no overlap)")

@@ -162,6 +162,11 @@ int vep_convert_batch_noalloc(const vep_frame_desc *descs, int n, void *cuda_str
  * until `ring_depth` newer frames of that stream have been converted (ring_depth + VEP_MAX_TICKS_IN_FLIGHT + 2
  * slots are kept per stream, each with pinned input, pinned output and device buffers). */
 int vep_stream_open(vep_ctx *ctx, int stream_id, int fmt, int width, int height, int ring_depth);
+/* Page-lock / release a range of host memory the caller owns (cudaHostRegister, usable from every GPU), e.g. the
+ * arena a decoder's get_buffer callback hands frames out of: once at start-up, not per frame (registering costs about
+ * a millisecond per 10 MB).  Unregister before freeing the memory. */
+int vep_host_register(void *ptr, size_t bytes);
+int vep_host_unregister(void *ptr);
 /* Not while ticks are in flight (VEP_ERR_BUSY) and not while another thread is inside a call for this stream. */
 int vep_stream_close(vep_ctx *ctx, int stream_id);
 /* Helper threads for the staging copy (default 0).  One core copies 10-16 GB/s into pinned memory, a PCIe Gen5
@@ -170,10 +175,21 @@ int vep_stream_close(vep_ctx *ctx, int stream_id);
  * covers them, as the reference's one process per camera does).  vep_submit_batch: all pieces of all frames. */
 int vep_set_staging_threads(vep_ctx *ctx, int n);
 
-/* Hand one decoded frame (HOST pointers: AVFrame planes + linesizes) to the library.  The planes
- * are copied into pinned staging before the call returns, so the caller's frame may be freed.
- * convert == 0 records a gate-skipped frame (counted, never copied).  Callable concurrently for
- * different streams; one producer per stream. */
+/* Hand one decoded frame (HOST pointers: AVFrame planes + linesizes) to the library.  `convert` is
+ *   VEP_SUBMIT_SKIP   (0) a gate-skipped frame: counted, never copied (read_image.py:80);
+ *   VEP_SUBMIT_COPY   (1) the planes are copied into pinned staging before the call returns, so the caller's frame
+ *                         may be freed at once (what PyAV's pageable frames need);
+ *   VEP_SUBMIT_PINNED (2) no CPU copy: the planes already lie in page-locked host memory (a decoder buffer pool
+ *                         registered once with vep_host_register, or any cudaHostAlloc'ed / cudaHostRegister'ed memory) and
+ *                         the tick's H2D copy reads them in place, any linesize.  The caller keeps them valid and unchanged
+ *                         until the tick that takes the frame has been waited for (vep_tick / vep_tick_wait*), i.e. it
+ *                         holds its AVFrame reference that long.  Refused with VEP_ERR_INVALID_ARG when a plane is not
+ *                         page-locked.  On a host whose memory system is shared by several GPUs' DMA traffic this is the
+ *                         difference between ~0.77 and ~0.98 of the box's DMA ceiling.
+ * Callable concurrently for different streams; one producer per stream. */
+#define VEP_SUBMIT_SKIP 0
+#define VEP_SUBMIT_COPY 1
+#define VEP_SUBMIT_PINNED 2
 int vep_submit(vep_ctx *ctx, int stream_id, const uint8_t *const plane[3], const int32_t stride[3],
                const vep_frame_meta *meta, int convert);
 /* The frames of one tick with ONE call (one item per camera, at most one frame per stream and call): the staging
@@ -183,7 +199,7 @@ int vep_submit(vep_ctx *ctx, int stream_id, const uint8_t *const plane[3], const
  * cannot be staged (its status is returned, *n_done = items staged and committed before it). */
 typedef struct {
     int32_t stream_id;
-    int32_t convert;
+    int32_t convert;           /* VEP_SUBMIT_SKIP / _COPY / _PINNED, as for vep_submit */
     const uint8_t *plane[3];   /* HOST pointers, as for vep_submit */
     int32_t stride[3];
     int32_t reserved;

@@ -564,3 +564,68 @@ def test_submit_many_stages_a_whole_tick_with_helper_threads(path):
     assert e.value.status == _abi.VEP_ERR_BUSY
     assert path.tick() == 7                                  # 6 frames of s0 + the one of s2 staged before the failure
     path.set_staging_threads(0)
+
+
+def test_pinned_submit_reads_the_callers_planes_in_place(path):
+    """VEP_SUBMIT_PINNED: frames that live in a registered (page-locked) decoder arena are converted without a CPU
+    copy, whatever their linesize; pageable planes are refused in that mode; the staging slot's own memory stays
+    untouched (sentinel) — proof that the H2D copy came from the caller's memory."""
+    cams = [("p%d" % i, fmt, w, h) for i, (fmt, w, h) in enumerate(
+        [("yuv420p", 1920, 1080), ("nv12", 1280, 720), ("yuv420p", 854, 480), ("yuvj422p", 640, 480), ("gray", 50, 6),
+         ("yuv420p10le", 640, 480), ("yuv444p", 130, 8)])]
+    arena = np.zeros(64 << 20, np.uint8)                     # the decoder's frame pool: one allocation, registered once
+    path.register_host(arena)
+    try:
+        off, frames, want = 0, [], {}
+        for i, (name, fmt, w, h) in enumerate(cams):
+            path.open_stream(name, fmt, w, h)
+            planes = make_planes(fmt, w, h, 60 + i)
+            views = []
+            for p in planes:                                 # decoder-style padded linesize (+32 bytes), 64-byte aligned planes
+                pb = p.view(np.uint8).reshape(p.shape[0], -1)
+                ls = pb.shape[1] + 32
+                a = arena[off:off + pb.shape[0] * ls].reshape(pb.shape[0], ls)
+                a[:, :pb.shape[1]] = pb
+                a[:, pb.shape[1]:] = 0xEE
+                views.append(a[:, :pb.shape[1]].view(p.dtype))
+                off = (off + a.size + 63) // 64 * 64
+            frames.append((name, views, make_meta(timestamp=i + 1)))
+            want[name] = F.to_bgr24(fmt, planes)
+        # poison the staging slots first: a pinned submit must not read them
+        for name, fmt, w, h in cams:
+            for v in path.acquire_input(name):
+                v[...] = 0x77 if v.dtype == np.uint8 else 0x0177
+            path.commit_input(name)
+        path.tick()
+        h2d0 = path.stats()["h2d_bytes"]
+        assert path.submit_many(frames, pinned=True) == len(cams)
+        assert path.tick() == len(cams)
+        moved = path.stats()["h2d_bytes"] - h2d0
+        visible = sum(sum(v.shape[0] * v.shape[1] * v.itemsize for v in f[1]) for f in frames)
+        assert visible <= moved <= visible * 1.6              # rows travel with the decoder's padding at most; never the staging slots
+        for name, w_ in want.items():
+            assert np.array_equal(path.result(name), w_), name
+        # single-frame call, and the frame may change once its tick has been waited for
+        name, views, meta = frames[0]
+        views[0][...] = 255 - views[0]
+        path.submit(name, views, meta, pinned=True)
+        path.tick()
+        assert np.array_equal(path.result(name), F.to_bgr24("yuv420p", views))
+        # pageable memory is refused in this mode, with the reason
+        with pytest.raises(VepError) as e:
+            path.submit("p0", make_planes("yuv420p", 1920, 1080, 1), None, pinned=True)
+        assert e.value.status == _abi.VEP_ERR_INVALID_ARG and "page-locked" in str(e.value)
+        assert path.tick() == 0
+    finally:
+        path.unregister_host(arena)
+
+
+def test_staged_bytes_is_what_a_tick_copies_in(path):
+    for i, (fmt, w, h) in enumerate([("yuv420p", 1920, 1080), ("nv12", 1366, 768), ("yuv420p", 854, 480), ("gray", 50, 6),
+                                     ("yuvj422p", 640, 480), ("yuv444p", 130, 8), ("yuv420p10le", 640, 480)]):
+        name = f"b{i}"
+        path.open_stream(name, fmt, w, h)
+        before = path.stats()["h2d_bytes"]
+        path.submit(name, make_planes(fmt, w, h, i))
+        path.tick()
+        assert path.stats()["h2d_bytes"] - before == path.staged_bytes(name), (fmt, w, h)

@@ -14,7 +14,7 @@ class _Path:
     def open_stream(self, device_id, fmt, w, h, ring):
         self.opened[device_id] = ring
 
-    def submit(self, device_id, planes, meta):
+    def submit(self, device_id, planes, meta, pinned=False):
         self.staged.setdefault(device_id, []).append(b"msg-%d" % meta.pts)
 
     def tick(self):

@@ -86,7 +86,7 @@ def test_idle_gops_are_skipped_and_activity_replays_the_gop_from_its_key_frame()
         def open_stream(self, *a):
             pass
 
-        def submit(self, device_id, planes, meta):
+        def submit(self, device_id, planes, meta, pinned=False):
             self.staged.append((meta.pts, meta.packet, meta.keyframe, bool(meta.is_keyframe)))
 
         def tick(self):

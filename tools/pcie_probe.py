@@ -91,10 +91,22 @@ if rank == 0:
     numa = os.popen("lscpu 2>/dev/null | grep -i -E 'numa|model name|^cpu\\(s\\)|socket'").read()
     print(json.dumps({"phase": "host", "n_gpus": world, "cores_visible": len(cores), "lscpu": numa.strip().splitlines(), "topo": topo.strip().splitlines()}), flush=True)
 
+if os.environ.get("PROBE_ONLY_MERGE"):      # short form: does the copy granularity move the box ceiling?
+    phase("frames_both", F_IN, F_OUT, note="16 + 16 copies per tick")
+    phase("tick_merged", [sum(F_IN)], [sum(F_OUT)], note="one 49.8 MB copy in + one 99.5 MB copy out per tick")
+    phase("tick_merged_4", [sum(F_IN) // 4] * 4, [sum(F_OUT) // 4] * 4, note="four copies per direction and tick")
+    if world > 1:
+        dist.destroy_process_group()
+    sys.exit(0)
 phase("h2d_only", [BIG], [])
 phase("d2h_only", [], [BIG])
 phase("both_large", [BIG], [BIG])
 phase("frames_both", F_IN, F_OUT, note="the 16 x 1080p tick; this is the e2e ceiling")
+if os.environ.get("PROBE_EXTRA"):
+    phase("frames_h2d_only", F_IN, [], note="16 x 3.1 MB per tick, H2D alone")
+    phase("frames_d2h_only", [], F_OUT, note="16 x 6.2 MB per tick, D2H alone")
+    phase("tick_merged", [sum(F_IN)], [sum(F_OUT)], note="one 49.8 MB copy in + one 99.5 MB copy out per tick")
+    phase("frames_3_copies_in", [2073600, 518400, 518400] * 16, F_OUT, note="H2D as three copies per frame (Y, U, V separately)")
 
 # ---- the same with each rank on its own cores ----
 per = max(1, len(cores) // world)

@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libvepb200.so")
 VEP_FMT = {"yuv420p": 0, "yuvj420p": 1, "nv12": 2, "nv21": 3, "yuv422p": 4, "yuvj422p": 5, "yuv420p10le": 6, "yuv444p": 7, "yuvj444p": 8, "gray": 9}
 VEP_OK, VEP_ERR_INVALID_ARG, VEP_ERR_GEOMETRY, VEP_ERR_CUDA = 0, -1, -2, -3
 VEP_ORDER_STRICT, VEP_ORDER_WRITES, VEP_ORDER_NONE = 0, 1, 2
+VEP_SUBMIT_SKIP, VEP_SUBMIT_COPY, VEP_SUBMIT_PINNED = 0, 1, 2
 VEP_ERR_NOMEM, VEP_ERR_STATE, VEP_ERR_NO_FRAME, VEP_ERR_BUSY = -4, -5, -6, -7
 
 
@@ -70,6 +71,8 @@ SIGNATURES = {
     "vep_stream_open": (_i, [_p, _i, _i, _i, _i, _i]),
     "vep_stream_close": (_i, [_p, _i]),
     "vep_set_staging_threads": (_i, [_p, _i]),
+    "vep_host_register": (_i, [_p, C.c_size_t]),
+    "vep_host_unregister": (_i, [_p]),
     "vep_submit": (_i, [_p, _i, C.POINTER(C.c_void_p * 3), C.POINTER(C.c_int32 * 3),
                         C.POINTER(FrameMeta), _i]),
     "vep_submit_batch": (_i, [_p, C.POINTER(SubmitItem), _i, _ip]),

@@ -186,6 +186,10 @@ struct Slot {
     int state = SLOT_FREE;
     size_t msg_off = 0, msg_len = 0;
     cudaEvent_t done = nullptr;
+    // VEP_SUBMIT_PINNED: the frame stays in the caller's page-locked planes until the tick copies it to the device
+    bool external = false;
+    const uint8_t *ext_plane[3] = {nullptr, nullptr, nullptr};
+    int32_t ext_stride[3] = {0, 0, 0};
 };
 
 struct Stream {
@@ -376,6 +380,17 @@ extern "C" int vep_create(int device, vep_ctx **out) {
     for (auto &t : c->tb) CUDA_TRY(cudaEventCreateWithFlags(&t.used, cudaEventDisableTiming));
     for (auto &t : c->ticks) { CUDA_TRY(cudaEventCreate(&t.k0)); CUDA_TRY(cudaEventCreate(&t.k1)); }
     *out = c;
+    return VEP_OK;
+}
+
+extern "C" int vep_host_register(void *ptr, size_t bytes) {
+    if (!ptr || !bytes) return fail(VEP_ERR_INVALID_ARG, "null pointer or zero length");
+    CUDA_TRY(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+    return VEP_OK;
+}
+extern "C" int vep_host_unregister(void *ptr) {
+    if (!ptr) return fail(VEP_ERR_INVALID_ARG, "null pointer");
+    CUDA_TRY(cudaHostUnregister(ptr));
     return VEP_OK;
 }
 
@@ -746,6 +761,7 @@ extern "C" int vep_acquire_input(vep_ctx *c, int stream_id, uint8_t *plane_out[3
     std::lock_guard<std::mutex> lk(s->mu);
     const int i = claim_slot(s);
     if (i < 0) return fail(VEP_ERR_BUSY, "stream %d: no free staging slot (tick more often or raise ring_depth)", stream_id);
+    s->slots[i].external = false;
     plane_ptrs(s, s->slots[i].h_in, plane_out, stride_out);
     return VEP_OK;
 }
@@ -827,22 +843,46 @@ static void add_plane_jobs(std::vector<CopyJob> &jobs, const PlaneCopy &p) {
     for (int r = 0; r < p.rows; r += rows_per) jobs.push_back(CopyJob{p, r, std::min(p.rows, r + rows_per)});
 }
 
-// validate one frame against its stream and claim its staging slot; fills the plane copies
-static int prepare_submit(vep_ctx *c, Stream *s, const uint8_t *const plane[3], const int32_t stride[3], PlaneCopy pc[3], int *np) {
+// page-locked (cudaHostAlloc'ed or cudaHostRegister'ed) host memory?  first and last byte of the range are asked for
+static bool range_is_pinned(const uint8_t *p, size_t bytes) {
+    for (const uint8_t *q : {p, p + (bytes ? bytes - 1 : 0)}) {
+        cudaPointerAttributes a{};
+        if (cudaPointerGetAttributes(&a, q) != cudaSuccess) { cudaGetLastError(); return false; }
+        if (a.type != cudaMemoryTypeHost) return false;
+    }
+    return true;
+}
+
+// validate one frame against its stream and claim its staging slot; fills the plane copies (mode VEP_SUBMIT_COPY) or
+// notes the caller's planes in the slot (VEP_SUBMIT_PINNED: *np = 0, nothing to copy)
+static int prepare_submit(vep_ctx *c, Stream *s, const uint8_t *const plane[3], const int32_t stride[3], PlaneCopy pc[3], int *np, int mode = VEP_SUBMIT_COPY) {
     const bool semi = vep::fmt_is_semiplanar(s->fmt), gray = s->fmt == VEP_FMT_GRAY8;
     if (!plane || !stride || !plane[0] || (!gray && (!plane[1] || (!semi && !plane[2])))) return fail(VEP_ERR_INVALID_ARG, "null plane");
     const int bps = vep::fmt_bytes_per_sample(s->fmt);
     const int cw = ((semi || vep::fmt_is_444(s->fmt)) ? s->w : s->w / 2) * bps;      // chroma row bytes
     const int crows = (vep::fmt_is_422(s->fmt) || vep::fmt_is_444(s->fmt)) ? s->h : s->h / 2;
     if (stride[0] < s->w * bps || (!gray && (stride[1] < cw || (!semi && stride[2] < cw)))) return fail(VEP_ERR_GEOMETRY, "stride smaller than row");
+    if (mode != VEP_SUBMIT_COPY && mode != VEP_SUBMIT_PINNED) return fail(VEP_ERR_INVALID_ARG, "unknown submit mode %d", mode);
+    if (mode == VEP_SUBMIT_PINNED) {
+        const int np_ = gray ? 1 : semi ? 2 : 3;
+        for (int i = 0; i < np_; ++i) {
+            const size_t rb = i == 0 ? (size_t)s->w * bps : (size_t)cw, rows = i == 0 ? (size_t)s->h : (size_t)crows;
+            if (!range_is_pinned(plane[i], (rows - 1) * (size_t)stride[i] + rb))
+                return fail(VEP_ERR_INVALID_ARG, "stream %d: plane %d is not in page-locked host memory (vep_host_register it, or submit with VEP_SUBMIT_COPY)", s->id, i);
+        }
+    }
     uint8_t *pl[3];
     int32_t st[3];
     {
         std::lock_guard<std::mutex> lk(s->mu);
         const int i = claim_slot(s);
         if (i < 0) return fail(VEP_ERR_BUSY, "stream %d: no free staging slot (tick more often or raise ring_depth)", s->id);
-        plane_ptrs(s, s->slots[i].h_in, pl, st);
+        Slot &sl = s->slots[i];
+        plane_ptrs(s, sl.h_in, pl, st);
+        sl.external = mode == VEP_SUBMIT_PINNED;
+        for (int k = 0; k < 3; ++k) { sl.ext_plane[k] = sl.external ? plane[k] : nullptr; sl.ext_stride[k] = sl.external ? stride[k] : 0; }
     }
+    if (mode == VEP_SUBMIT_PINNED) { *np = 0; return VEP_OK; }
     int n = 0;
     pc[n++] = PlaneCopy{pl[0], st[0], plane[0], stride[0], s->w * bps, s->h};
     if (!gray) pc[n++] = PlaneCopy{pl[1], st[1], plane[1], stride[1], cw, crows};
@@ -862,7 +902,7 @@ extern "C" int vep_submit(vep_ctx *c, int stream_id, const uint8_t *const plane[
     }
     PlaneCopy pc[3];
     int np = 0;
-    int rc = prepare_submit(c, s, plane, stride, pc, &np);
+    int rc = prepare_submit(c, s, plane, stride, pc, &np, convert);
     if (rc) return rc;
     // the copy runs outside the lock (one producer per stream); a large frame is shared with the helper threads
     size_t total = 0;
@@ -892,7 +932,7 @@ extern "C" int vep_submit_batch(vep_ctx *c, const vep_submit_item *items, int n,
         if (!it.convert) continue;
         PlaneCopy pc[3];
         int np = 0;
-        rc = prepare_submit(c, s, it.plane, it.stride, pc, &np);
+        rc = prepare_submit(c, s, it.plane, it.stride, pc, &np, it.convert);
         if (rc) break;
         for (int i = 0; i < np; ++i) add_plane_jobs(jobs, pc[i]);
     }
@@ -964,11 +1004,37 @@ static int tick_enqueue(vep_ctx *c, TickRec &t, int *n_frames) {
             const int i = ((s->wr - k) % ns + ns) % ns;
             Slot &sl = s->slots[i];
             if (sl.state != SLOT_SUBMITTED) continue;
-            CUDA_TRY(cudaMemcpyAsync(sl.d_in, sl.h_in, s->in_bytes, cudaMemcpyHostToDevice, s->cs_in));
-            c->stats.h2d_bytes += (int64_t)s->in_bytes;
             vep_frame_desc d{};
             uint8_t *pl[3];
             plane_ptrs(s, sl.d_in, pl, d.stride);
+            if (!sl.external) {
+                CUDA_TRY(cudaMemcpyAsync(sl.d_in, sl.h_in, s->in_bytes, cudaMemcpyHostToDevice, s->cs_in));
+                c->stats.h2d_bytes += (int64_t)s->in_bytes;
+            } else {
+                // Straight from the caller's page-locked planes.  A plane whose linesize is a multiple of 16 and fits the
+                // slot goes over as ONE linear copy, padding included, and the kernel is told the caller's linesize
+                // (decoders pad linesizes to 32/64 bytes, so this is the usual case); any other linesize is re-pitched
+                // by the copy engine (row-wise DMA: slow for narrow rows, but correct for every layout).
+                const int bps = vep::fmt_bytes_per_sample(s->fmt);
+                const bool semi = vep::fmt_is_semiplanar(s->fmt);
+                const size_t crow = ((semi || vep::fmt_is_444(s->fmt)) ? (size_t)s->w : (size_t)s->w / 2) * bps;
+                const size_t crows = (vep::fmt_is_422(s->fmt) || vep::fmt_is_444(s->fmt)) ? (size_t)s->h : (size_t)s->h / 2;
+                const size_t region_end[3] = {s->fmt == VEP_FMT_GRAY8 ? s->in_slot : s->off_c0, semi ? s->in_slot : s->off_c1, s->in_slot};
+                const size_t region_begin[3] = {0, s->off_c0, s->off_c1};
+                for (int k = 0; k < 3; ++k) {
+                    if (!pl[k]) continue;
+                    const size_t rb = k == 0 ? (size_t)s->w * bps : crow, rows = k == 0 ? (size_t)s->h : crows;
+                    const size_t ls = (size_t)sl.ext_stride[k], span = (rows - 1) * ls + rb;
+                    if (ls % 16 == 0 && span <= region_end[k] - region_begin[k]) {
+                        CUDA_TRY(cudaMemcpyAsync(pl[k], sl.ext_plane[k], span, cudaMemcpyHostToDevice, s->cs_in));
+                        d.stride[k] = (int32_t)ls;
+                        c->stats.h2d_bytes += (int64_t)span;
+                    } else {
+                        CUDA_TRY(cudaMemcpy2DAsync(pl[k], d.stride[k], sl.ext_plane[k], ls, rb, rows, cudaMemcpyHostToDevice, s->cs_in));
+                        c->stats.h2d_bytes += (int64_t)(rb * rows);
+                    }
+                }
+            }
             d.plane[0] = pl[0]; d.plane[1] = pl[1]; d.plane[2] = pl[2];
             d.dst = sl.d_out; d.dst_stride = s->pitch_out; d.width = s->w; d.height = s->h; d.fmt = s->fmt; d.convert = 1;
             descs.push_back(d);

@@ -197,29 +197,42 @@ class FramePath:
 
     # ---- per-frame -----------------------------------------------------------------------------
     def submit(self, device_id: str, planes: Sequence[np.ndarray], meta: Optional[FrameMeta] = None,
-               convert: bool = True):
+               convert: bool = True, pinned: bool = False):
         """Stage one decoded frame (host planes, any row stride).  ctypes drops the GIL for the
-        copy, so one producer thread per camera scales like the reference's one process per camera."""
+        copy, so one producer thread per camera scales like the reference's one process per camera.
+        pinned=True (VEP_SUBMIT_PINNED): the planes lie in page-locked memory (see register_host) and are NOT
+        copied — keep them alive and unchanged until the tick that converts them has been waited for."""
         sid = self._sid(device_id)
         if not convert:
             check(self._L.vep_submit(self._ctx, sid, None, None, None, 0), "vep_submit")
             return
         ptrs, strides = _plane_ptrs(planes)
         check(self._L.vep_submit(self._ctx, sid, C.byref(ptrs), C.byref(strides),
-                                 C.byref(meta) if meta is not None else None, 1), "vep_submit")
+                                 C.byref(meta) if meta is not None else None,
+                                 _abi.VEP_SUBMIT_PINNED if pinned else _abi.VEP_SUBMIT_COPY), "vep_submit")
 
-    def submit_many(self, frames) -> int:
+    @staticmethod
+    def register_host(buf: np.ndarray):
+        """Page-lock the memory of `buf` (a contiguous array a decoder's frames live in) so that frames inside it can
+        be submitted with pinned=True.  Once per buffer, not per frame; unregister_host before the array is freed."""
+        check(_abi.lib().vep_host_register(C.c_void_p(buf.ctypes.data), C.c_size_t(buf.nbytes)), "vep_host_register")
+
+    @staticmethod
+    def unregister_host(buf: np.ndarray):
+        check(_abi.lib().vep_host_unregister(C.c_void_p(buf.ctypes.data)), "vep_host_unregister")
+
+    def submit_many(self, frames, pinned: bool = False) -> int:
         """Stage the frames of one tick with ONE call: `frames` is a sequence of (device_id, planes, meta) — at most
         one per camera — or (device_id, None, None) for a gate-skipped frame.  The copies are shared between this
-        thread and the helper threads of set_staging_threads().  Returns the number of items staged; raises on the
-        first one that could not be."""
+        thread and the helper threads of set_staging_threads(); with pinned=True nothing is copied (see submit).
+        Returns the number of items staged; raises on the first one that could not be."""
         arr = (_abi.SubmitItem * len(frames))()
         for it, (device_id, planes, meta) in zip(arr, frames):
             it.stream_id = self._sid(device_id)
             if planes is None:
                 it.convert = 0
                 continue
-            it.convert = 1
+            it.convert = _abi.VEP_SUBMIT_PINNED if pinned else _abi.VEP_SUBMIT_COPY
             for i, p in enumerate(planes):
                 if p.dtype not in (np.uint8, np.uint16) or p.ndim != 2 or p.strides[1] != p.itemsize:
                     raise ValueError("planes must be 2-D uint8 (uint16 for 10-bit formats) arrays with contiguous rows")
@@ -246,6 +259,20 @@ class FramePath:
             rows = np.frombuffer(buf, np.uint8).reshape(shp[0], strides[i])
             out.append(rows.view(np.uint16)[:, :shp[1]] if fmt == "yuv420p10le" else rows[:, :shp[1]])
         return out
+
+    def staged_bytes(self, device_id: str) -> int:
+        """Bytes one staged frame of this camera occupies in its pinned slot = what the tick's H2D copy moves
+        (planes with rows padded to 16-byte pitches where the width needs it, planes 256-byte aligned)."""
+        fmt, w, h = self._geom[device_id]
+        bps = 2 if fmt == "yuv420p10le" else 1
+        pitch = lambda rb: rb if rb % 16 == 0 else (rb + 63) // 64 * 64
+        a256 = lambda v: (v + 255) // 256 * 256
+        ysz = pitch(w * bps) * h
+        if fmt == "gray":
+            return ysz
+        semi, c444, c422 = fmt in ("nv12", "nv21"), fmt in ("yuv444p", "yuvj444p"), fmt in ("yuv422p", "yuvj422p")
+        csz = pitch((w if (semi or c444) else w // 2) * bps) * (h if (c422 or c444) else h // 2)
+        return a256(ysz) + csz if semi else a256(ysz) + a256(csz) + csz
 
     def acquire_raw(self, device_id: str):
         """(pointers, strides) of the next pinned staging slot as ctypes arrays — for producers that hand the

@@ -38,11 +38,16 @@ class _Camera:
 
 
 class FrameProducer:
-    def __init__(self, path: FramePath, redis_conn, now_ms=None):
+    def __init__(self, path: FramePath, redis_conn, now_ms=None, pinned_frames: bool = False):
+        """pinned_frames=True: the decoder hands out frames whose planes lie in page-locked memory (its buffer pool
+        was registered with FramePath.register_host); they are submitted without a CPU copy (VEP_SUBMIT_PINNED) and
+        this object keeps a reference to every such frame until the tick that converts it has finished."""
         self.path = path
         self.redis = redis_conn
         self._cams: Dict[str, _Camera] = {}
         self._now_ms = now_ms or (lambda: int(round(time.time() * 1000)))
+        self._pinned = bool(pinned_frames)
+        self._held: List[object] = []      # frames the GPU may still read (pinned_frames only)
 
     def add_camera(self, device_id: str, fmt: str, width: int, height: int, memory_buffer: int = 1):
         # the library keeps min(memory_buffer, 64) frames readable; XADD MAXLEN carries the full value
@@ -91,12 +96,14 @@ class FrameProducer:
                              is_keyframe=o.is_keyframe, is_corrupt=o.is_corrupt,
                              frame_type=getattr(frame.pict_type, "name", frame.pict_type))
             try:
-                self.path.submit(device_id, frame.planes, meta)
+                self.path.submit(device_id, frame.planes, meta, pinned=self._pinned)
             except VepError as e:
                 if e.status != VEP_ERR_BUSY:
                     raise
                 self.flush()      # a long catch-up burst filled this camera's staging ring:
-                self.path.submit(device_id, frame.planes, meta)   # convert + publish, then go on
+                self.path.submit(device_id, frame.planes, meta, pinned=self._pinned)   # convert + publish, then go on
+            if self._pinned:
+                self._held.append(frame)
             cam.staged += 1
             staged += 1
             if o.first_frame_only:
@@ -110,6 +117,7 @@ class FrameProducer:
         queued on ONE non-transactional pipeline and sent with one `execute()`, i.e. one round trip per tick
         instead of one per message.  Connections without `pipeline()` get the direct calls."""
         n = self.path.tick()
+        self._held.clear()       # the tick has read every submitted plane
         make_pipe = getattr(self.redis, "pipeline", None)
         sink = make_pipe(transaction=False) if make_pipe is not None else self.redis
         queued = 0
