@@ -629,3 +629,64 @@ def test_staged_bytes_is_what_a_tick_copies_in(path):
         path.submit(name, make_planes(fmt, w, h, i))
         path.tick()
         assert path.stats()["h2d_bytes"] - before == path.staged_bytes(name), (fmt, w, h)
+
+
+def test_stream_groups_move_a_lock_step_fleet_with_one_copy_per_direction(path):
+    """vep_stream_open_many: slots laid out [slot][camera]; neighbours that tick in lock step ride in one H2D and one D2H
+    copy.  Results, packed messages (the framing is written after the merged copy swept its room) and copy counts."""
+    cams = [("g%d" % i, fmt, w, h) for i, (fmt, w, h) in enumerate(
+        [("yuv420p", 1920, 1080)] * 3 + [("nv12", 1280, 720)] * 2 + [("yuv420p", 854, 480)] + [("yuvj420p", 640, 480)] * 2)]
+    path.open_streams(cams, memory_buffer=2)
+    VideoFrame, _ = W.dynamic_message_class()
+
+    def tick(selected, seed):
+        frames, want = [], {}
+        for name, fmt, w, h in cams:
+            if name not in path.streams():
+                continue
+            if name in selected:
+                planes = make_planes(fmt, w, h, seed + len(frames))
+                frames.append((name, planes, make_meta(timestamp=seed, pts=seed + 1, packet=len(frames), frame_type="P")))
+                want[name] = (F.to_bgr24(fmt, planes), seed)
+            else:
+                frames.append((name, None, None))
+        s0 = path.stats()
+        path.submit_many(frames)
+        assert path.tick() == len(selected)
+        s1 = path.stats()
+        for name, (img, sd) in want.items():
+            assert np.array_equal(path.result(name), img), name
+            vf = VideoFrame(); vf.ParseFromString(bytes(path.result_packed(name)))
+            assert vf.data == img.tobytes() and vf.timestamp == sd and vf.pts == sd + 1 and vf.frame_type == "P"
+            assert [(d.size, d.name) for d in vf.shape.dim] == [(img.shape[0], "0"), (img.shape[1], "1"), (3, "2")]
+        return s1["copies_in"] - s0["copies_in"], s1["copies_out"] - s0["copies_out"]
+
+    names = [c[0] for c in cams]
+    # all eight in lock step: one copy in; out: the 854-wide camera (padded device rows, 2-D copy) splits the run in three
+    assert tick(set(names), 100) == (1, 3)
+    assert tick(set(names), 200) == (1, 3)
+    # cameras 0-4 only: one run each way
+    assert tick(set(names[:5]), 300) == (1, 1)
+    # a gap splits the run: {0,1} and {3,4}; then they are out of step with 2 by one slot, and stay split
+    assert tick({names[0], names[1], names[3], names[4]}, 400) == (2, 2)
+    ci, co = tick(set(names[:5]), 500)
+    assert (ci, co) == (3, 3)                               # {0,1}, {2}, {3,4}: camera 2 sits one slot index behind
+    # a burst: two frames of one camera in one tick (different slot indices), neighbours one each
+    planes_a, planes_b = make_planes("yuv420p", 1920, 1080, 601), make_planes("yuv420p", 1920, 1080, 602)
+    path.submit(names[0], planes_a, make_meta(timestamp=1))
+    path.submit(names[0], planes_b, make_meta(timestamp=2))
+    path.submit(names[1], planes_a, make_meta(timestamp=3))
+    assert path.tick() == 3
+    assert np.array_equal(path.result(names[0]), F.to_bgr24("yuv420p", planes_b))
+    assert np.array_equal(path.result(names[0], age=1), F.to_bgr24("yuv420p", planes_a))
+    assert np.array_equal(path.result(names[1]), F.to_bgr24("yuv420p", planes_a))
+    # members close one by one; the shared memory goes with the last; the names can be opened again
+    for n in names:
+        path.close_stream(n)
+    path.open_streams(cams[:2])
+    assert tick({names[0], names[1]}, 700) == (1, 1)
+    with pytest.raises(VepError):
+        path.open_streams([("dup", "yuv420p", 64, 48), ("dup", "yuv420p", 64, 48)])
+    with pytest.raises(VepError):
+        path.open_streams([("ok", "yuv420p", 64, 48), ("bad", "nv12", 64, 6)])
+    assert "ok" not in path.streams()

@@ -42,7 +42,12 @@ class Stats(C.Structure):
     _fields_ = [("frames_offered", C.c_int64), ("frames_converted", C.c_int64),
                 ("ticks", C.c_int64), ("kernel_launches", C.c_int64),
                 ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
-                ("last_kernel_ms", C.c_float)]
+                ("last_kernel_ms", C.c_float), ("reserved", C.c_int32),
+                ("copies_in", C.c_int64), ("copies_out", C.c_int64)]
+
+
+class StreamSpec(C.Structure):
+    _fields_ = [("stream_id", C.c_int32), ("fmt", C.c_int32), ("width", C.c_int32), ("height", C.c_int32)]
 
 
 _p = C.c_void_p
@@ -69,6 +74,7 @@ SIGNATURES = {
     "vep_plan_info": (_i, [_p, _ip, _ip, C.POINTER(C.c_int64)]),
     "vep_plan_destroy": (None, [_p]),
     "vep_stream_open": (_i, [_p, _i, _i, _i, _i, _i]),
+    "vep_stream_open_many": (_i, [_p, C.POINTER(StreamSpec), _i, _i]),
     "vep_stream_close": (_i, [_p, _i]),
     "vep_set_staging_threads": (_i, [_p, _i]),
     "vep_host_register": (_i, [_p, C.c_size_t]),

@@ -182,6 +182,23 @@ class FramePath:
         self._ids[device_id] = sid
         self._geom[device_id] = (fmt, width, height)
 
+    def open_streams(self, cameras, memory_buffer: int = 1):
+        """Declare several cameras at once: `cameras` = [(device_id, fmt, width, height), ...].  Their slots share one
+        allocation laid out [slot][camera], so cameras that are neighbours in the list and tick in lock step are copied to
+        and from the GPU with one copy per direction for the whole run (vep_stream_open_many)."""
+        specs = (_abi.StreamSpec * len(cameras))()
+        for i, (device_id, fmt, w, h) in enumerate(cameras):
+            if device_id in self._ids or device_id in [c[0] for c in cameras[:i]]:
+                raise VepError(_abi.VEP_ERR_STATE, "open_streams", f"{device_id!r} already open")
+            if fmt not in VEP_FMT:
+                raise VepError(_abi.VEP_ERR_INVALID_ARG, "open_streams", f"unknown format {fmt!r}")
+            specs[i].stream_id, specs[i].fmt, specs[i].width, specs[i].height = self._next_id + i, VEP_FMT[fmt], w, h
+        check(self._L.vep_stream_open_many(self._ctx, specs, len(cameras), memory_buffer), "vep_stream_open_many")
+        for i, (device_id, fmt, w, h) in enumerate(cameras):
+            self._ids[device_id] = self._next_id + i
+            self._geom[device_id] = (fmt, w, h)
+        self._next_id += len(cameras)
+
     def close_stream(self, device_id: str):
         check(self._L.vep_stream_close(self._ctx, self._sid(device_id)), "vep_stream_close")
         del self._ids[device_id], self._geom[device_id]

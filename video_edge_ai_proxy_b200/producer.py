@@ -54,6 +54,14 @@ class FrameProducer:
         self.path.open_stream(device_id, fmt, width, height, max(1, min(int(memory_buffer), MAX_RING_DEPTH)))
         self._cams[device_id] = _Camera(memory_buffer)
 
+    def add_cameras(self, cameras, memory_buffer: int = 1):
+        """Several cameras at once — [(device_id, fmt, width, height), ...] — with shared slot memory, so that a fleet
+        whose cameras convert in lock step is copied to and from the GPU with one copy per direction per tick
+        (FramePath.open_streams)."""
+        self.path.open_streams(list(cameras), max(1, min(int(memory_buffer), MAX_RING_DEPTH)))
+        for device_id, _fmt, _w, _h in cameras:
+            self._cams[device_id] = _Camera(memory_buffer)
+
     def on_packet(self, device_id: str, packet, control: Optional[CameraControl] = None) -> int:
         """Feed one demuxed packet of a camera.  Returns how many frames were staged for the next
         flush().  `control` carries the camera's Redis control state (gate.poll_control).
