@@ -1,5 +1,5 @@
 #!/bin/bash
-# round 2, one GPU: tests, smoke, the two arms as the driver runs them, every workload, launch list
+# round 2, one GPU: tests, smoke, the two arms as the driver runs them, every workload, launch list, soak, tick kernel time
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q > gpurun_out/r2f1_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/r2f1_pytest.log
 tail -3 gpurun_out/r2f1_pytest.log
@@ -11,3 +11,5 @@ for wl in 1x480p 8x1080p 8x4k-nv12 8x4k-nv12-keyframe mixed128-skip 16x854x480 1
 python bench.py --gpus 1 --steps 300 --warmup 5 --workload $wl > gpurun_out/r2f1_bench_$wl.json 2> gpurun_out/r2f1_bench_$wl.err; echo "$wl rc=$?"
 done
 python bench.py --gpus 1 --steps 300 --warmup 5 --workload 1x480p --impl reference > gpurun_out/r2f1_ref_1x480p.json 2>/dev/null
+python tools/tick_kernel_ms.py > gpurun_out/r2f1_tick_kernel_ms.log 2>&1; cat gpurun_out/r2f1_tick_kernel_ms.log | tail -4
+python tools/soak.py 40 > gpurun_out/r2f1_soak.log 2>&1; tail -1 gpurun_out/r2f1_soak.log

@@ -21,17 +21,24 @@ while time.time() < t_end:
     names = []
     for c in range(6):
         fmt = fmts[(it + c) % len(fmts)]
-        w, h = [(640, 480), (1280, 720), (50, 10), (1920, 1080)][(it + c) % 4]
-        nm = f"s{it}_{c}"
-        path.open_stream(nm, fmt, w, h, memory_buffer=2)
-        names.append((nm, fmt, w, h))
+        w, h = [(640, 480), (1280, 720), (50, 10), (1920, 1080), (854, 480)][(it + c) % 5]
+        names.append((f"s{it}_{c}", fmt, w, h))
+    if it % 2:                                     # alternately one by one and as a group with shared slot memory
+        for nm, fmt, w, h in names:
+            path.open_stream(nm, fmt, w, h, memory_buffer=2)
+    else:
+        path.open_streams(names, memory_buffer=2)
+    path.set_staging_threads(it % 3)
     for k in range(20):
         for nm, fmt, w, h in names:
             key = (fmt, w, h, k % 3)
             if key not in want:
                 want[key] = (make_planes(fmt, w, h, k % 3), None)
                 want[key] = (want[key][0], F.to_bgr24(fmt, want[key][0]))
-            path.submit(nm, want[key][0], make_meta(packet=k))
+            if k % 4 != 3:
+                path.submit(nm, want[key][0], make_meta(packet=k))
+        if k % 4 == 3:                             # every fourth tick through the batch call
+            path.submit_many([(nm, want[(fmt, w, h, k % 3)][0], make_meta(packet=k)) for nm, fmt, w, h in names])
         path.tick_begin()
         if k % 2:
             path.tick_wait(); path.tick_wait()
