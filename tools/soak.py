@@ -13,7 +13,9 @@ rng = np.random.default_rng(0)
 path = FramePath(0)
 want = {}
 def free_mb(): return torch.cuda.mem_get_info()[0] / 1e6
-def rss_mb(): return resource.getrusage(resource.RUSAGE_SELF).ru_maxrss / 1e3
+def rss_mb():      # CURRENT resident set (not the peak): sampled after every stream of the iteration has been closed
+    with open("/proc/self/statm") as f:
+        return int(f.read().split()[1]) * os.sysconf("SC_PAGE_SIZE") / 1e6
 t_end = time.time() + secs
 it = ticks = 0
 base_free = base_rss = None
@@ -55,8 +57,8 @@ while time.time() < t_end:
     for nm, *_ in names:
         path.close_stream(nm)
     it += 1
-    if it == 3:
+    if it == 40:       # past every (format, size, group/single) combination's first use: allocator pools have their final size
         torch.cuda.empty_cache(); base_free, base_rss = free_mb(), rss_mb()
 torch.cuda.empty_cache()
-print(f"SOAK iterations={it} ticks={ticks} device_free_delta_mb={free_mb() - base_free:.1f} host_rss_delta_mb={rss_mb() - base_rss:.1f}")
+print(f"SOAK iterations={it} ticks={ticks} device_free_delta_mb={free_mb() - base_free:.1f} host_rss_delta_mb={rss_mb() - base_rss:.1f} (current RSS after close, iteration 40 -> {it})")
 path.close()

@@ -55,6 +55,16 @@ for label, cams in SHAPES:
             launch_sequence([plan] * 200, st, order, e0.cuda_event, e1.cuda_event)
             torch.cuda.synchronize()
             res[nm] = e0.elapsed_time(e1) / 200
+        # one launch at a time after the GPU sat idle for 2 ms (what the PCIe-bound tick pipeline looks like to the SMs)
+        import time
+        idle = []
+        for _ in range(30):
+            torch.cuda.synchronize(); time.sleep(0.002)
+            launch_sequence([plan], st, _abi.VEP_ORDER_STRICT, e0.cuda_event, e1.cuda_event)
+            torch.cuda.synchronize()
+            idle.append(e0.elapsed_time(e1))
+        res["idle"] = statistics.median(idle)
         plan.close()
+        print(f"  the same plan, one launch after 2 ms of idle GPU: {res['idle'] * 1e3:.1f} us")
         print(f"{label}: kernel inside the tick {tick_ms * 1e3:.1f} us = {alg / tick_ms / 1e6:.0f} GB/s algorithmic; "
               f"plan back to back: strict {res['strict'] * 1e3:.1f} us ({alg / res['strict'] / 1e6:.0f} GB/s), no order {res['none'] * 1e3:.1f} us ({alg / res['none'] / 1e6:.0f} GB/s)")
