@@ -113,3 +113,33 @@ def test_frame_producer_publishes_the_reference_messages(trace, path, pipelined)
         assert [c for c in r.calls if c[0] == "cam-" + name] == _want(t), name
         assert r.streams.get("cam-" + name, []) == t["stream_after"], name
         assert [p.decode_calls for p in packets[name]] == t["decode_calls"], name
+
+
+def test_two_read_image_threads_share_one_frame_path(trace, path):
+    """Two `ReadImage` objects of one process on ONE FramePath, each fed from its own thread (the deployment
+    INTEGRATION.md describes for batching cameras in one process): every camera still publishes exactly the reference's
+    messages — a tick waits for the tick it began, whoever else ticks."""
+    picks = ["query_mid_gop_burst", "multi_frame_packets"]
+    results, errors = {}, []
+
+    def camera(name):
+        try:
+            sc = RS.scenarios()[name]
+            r = _Redis(pipelined=False)
+            ri = ReadImage(queue.Queue(), "cam2-" + name, sc["memory_buffer"], r, threading.Event(), threading.Condition(), frame_path=path)
+            for _ in range(3):            # three passes over the script: more interleavings
+                ri._gate.__init__()
+                r.calls.clear(); r.streams.clear()
+                for pkt, (_kf, _c, kfo, query, _n) in zip(RS.packets_of(sc), sc["events"]):
+                    r.kv[global_vars.RedisIsKeyFrameOnlyPrefix + "cam2-" + name] = b"true" if kfo else b"false"
+                    ri.process_packet(pkt, query_timestamp=query)        # per-camera query stamp: the threads run freely
+                results[name] = [(k.replace("cam2-", "cam-"), m, h, n) for k, m, h, n in r.calls]
+        except Exception as e:      # pragma: no cover
+            errors.append((name, repr(e)))
+
+    th = [threading.Thread(target=camera, args=(n,)) for n in picks]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errors, errors
+    for name in picks:
+        assert results[name] == _want(trace[name]), name

@@ -82,3 +82,21 @@ def test_bench_schedules_match_the_baseline_configs():
     assert bench.schedule_for("16x1080p", 16) == [list(range(16))]
     a, b = bench.cameras_for_rank("16x1080p", 0, 2), bench.cameras_for_rank("16x1080p", 1, 2)
     assert {c["camera"] for c in a}.isdisjoint({c["camera"] for c in b}) and len(a) == len(b) == 16
+
+
+def test_both_bench_arms_print_the_same_config_object_and_ranks_get_disjoint_cores():
+    import bench
+    for wl in ("16x1080p", "8x4k-nv12-keyframe", "mixed128-skip"):
+        a, b = bench.config_for(wl, 20), bench.config_for(wl, 20)
+        assert a == b and set(a) == {"workload", "cameras_per_gpu", "format", "converted_frames_per_step_per_gpu", "parallelism", "l2"}
+    assert bench.config_for("8x4k-nv12-keyframe", 30)["converted_frames_per_step_per_gpu"] == round(8 / 30, 3)
+    # core pinning: a child process per "rank" so this process keeps its own mask
+    code = ("import os,sys,json; sys.path.insert(0,%r); import bench; "
+            "print(json.dumps(bench.pin_rank_cores(int(sys.argv[1]), int(sys.argv[2]))))" % ROOT)
+    import json
+    n = len(os.sched_getaffinity(0))
+    world = 2 if n >= 2 else 1
+    sets = [json.loads(subprocess.run([sys.executable, "-c", code, str(r), str(world)], capture_output=True, text=True).stdout) for r in range(world)]
+    if world == 2:
+        assert sets[0] and sets[1] and set(sets[0]).isdisjoint(sets[1]) and len(sets[0]) == len(sets[1]) == n // 2
+    assert bench.pin_rank_cores(0, 1) is None          # a single rank is left alone

@@ -98,13 +98,16 @@ class ReadImage(threading.Thread):
             self._path.open_stream(self.device_id, fmt, w, h, min(max(int(self._memory_buffer), 1), 64))
             self._opened = (fmt, w, h)
 
-    def process_packet(self, packet):
-        """Body of the reference loop for one popped packet (read_image.py:61-128)."""
+    def process_packet(self, packet, query_timestamp=None):
+        """Body of the reference loop for one popped packet (read_image.py:61-128).  `query_timestamp`: this camera's
+        last client query; by default the module global the reference's producer thread sets (one camera per process
+        there) — a process that serves several cameras passes each camera's own value."""
         decode_only_keyframes = self.check_decode_only_keyframes()
         if packet.is_keyframe:
             self.packet_group = []
         self.packet_group.append(packet)
-        query_timestamp = global_vars.query_timestamp
+        if query_timestamp is None:
+            query_timestamp = global_vars.query_timestamp
         orders = self._gate.on_packet(packet.is_keyframe, packet.is_corrupt, decode_only_keyframes, query_timestamp)
         for o in orders:
             for frame in self.packet_group[o.group_index].decode() or ():
