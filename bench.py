@@ -619,6 +619,8 @@ def run_gpu(args):
             helpers = max(0, min(3, share - 2)) if args.staging_threads < 0 else args.staging_threads
         pool = ThreadPoolExecutor(n_prod)
         path.set_staging_threads(helpers)
+        if args.run_limit >= 0:
+            path.set_copy_run_limit(args.run_limit)
 
         class _Done:                      # a finished "future" for work done inline
             def result(self):
@@ -811,6 +813,7 @@ def main():
     ap.add_argument("--no-ceiling", action="store_true", help="skip the DMA ceiling probe")
     ap.add_argument("--e2e-only", action="store_true", help="diagnostic: skip the device-resident legs")
     ap.add_argument("--skip-e2e", action="store_true", help="diagnostic: skip the end-to-end legs")
+    ap.add_argument("--run-limit", type=int, default=-1, help="diagnostic: most frames per merged H2D/D2H copy (library default: no limit)")
     ap.add_argument("--staging-threads", type=int, default=-1, help="library helper threads for the staging copy (default: by this rank's share of the cores)")
     ap.add_argument("--pool", default="register", choices=["register", "alloc"], help="how the producer's frame pool of the e2e leg is page-locked")
     ap.add_argument("--e2e-submit", default="batch", choices=["batch", "threads"],

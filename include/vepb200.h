@@ -170,6 +170,9 @@ int vep_stream_open(vep_ctx *ctx, int stream_id, int fmt, int width, int height,
  * A member is closed with vep_stream_close; the memory is released with the last member. */
 typedef struct { int32_t stream_id, fmt, width, height; } vep_stream_spec;
 int vep_stream_open_many(vep_ctx *ctx, const vep_stream_spec *specs, int n, int ring_depth);
+/* The most frames one such merged copy may carry (0, the default: no limit; 1: one copy per frame as for cameras
+ * opened singly).  A run longer than the limit is cut into several copies, each on its first camera's streams. */
+int vep_set_copy_run_limit(vep_ctx *ctx, int max_frames_per_copy);
 /* Page-lock / release a range of host memory the caller owns (cudaHostRegister, usable from every GPU), e.g. the
  * arena a decoder's get_buffer callback hands frames out of: once at start-up, not per frame (registering costs about
  * a millisecond per 10 MB).  Unregister before freeing the memory. */

@@ -665,6 +665,9 @@ def test_stream_groups_move_a_lock_step_fleet_with_one_copy_per_direction(path):
     # all eight in lock step: one copy in; out: the 854-wide camera (padded device rows, 2-D copy) splits the run in three
     assert tick(set(names), 100) == (1, 3)
     assert tick(set(names), 200) == (1, 3)
+    path.set_copy_run_limit(2)                              # at most two cameras per copy: {0,1} {2,3} {4,5} {6,7} in; {4} and {5} split out
+    assert tick(set(names), 250) == (4, 5)
+    path.set_copy_run_limit(0)
     # cameras 0-4 only: one run each way
     assert tick(set(names[:5]), 300) == (1, 1)
     # a gap splits the run: {0,1} and {3,4}; then they are out of step with 2 by one slot, and stay split

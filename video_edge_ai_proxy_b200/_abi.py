@@ -77,6 +77,7 @@ SIGNATURES = {
     "vep_stream_open_many": (_i, [_p, C.POINTER(StreamSpec), _i, _i]),
     "vep_stream_close": (_i, [_p, _i]),
     "vep_set_staging_threads": (_i, [_p, _i]),
+    "vep_set_copy_run_limit": (_i, [_p, _i]),
     "vep_host_register": (_i, [_p, C.c_size_t]),
     "vep_host_unregister": (_i, [_p]),
     "vep_submit": (_i, [_p, _i, C.POINTER(C.c_void_p * 3), C.POINTER(C.c_int32 * 3),

@@ -281,6 +281,7 @@ struct vep_ctx {
     std::vector<uint8_t> tick_blob;
     StagePool pool;
     int stage_threads = 0;                          // helpers besides the submitting thread
+    int run_limit = 0;                              // most frames one merged copy may carry (0: no limit)
 };
 
 struct vep_plan {
@@ -401,6 +402,14 @@ extern "C" int vep_host_register(void *ptr, size_t bytes) {
 extern "C" int vep_host_unregister(void *ptr) {
     if (!ptr) return fail(VEP_ERR_INVALID_ARG, "null pointer");
     CUDA_TRY(cudaHostUnregister(ptr));
+    return VEP_OK;
+}
+
+extern "C" int vep_set_copy_run_limit(vep_ctx *c, int max_frames_per_copy) {
+    if (!c) return fail(VEP_ERR_INVALID_ARG, "ctx is null");
+    if (max_frames_per_copy < 0) return fail(VEP_ERR_INVALID_ARG, "limit %d < 0", max_frames_per_copy);
+    std::lock_guard<std::mutex> lk(c->mu);
+    c->run_limit = max_frames_per_copy;
     return VEP_OK;
 }
 
@@ -1141,9 +1150,12 @@ static int tick_enqueue(vep_ctx *c, TickRec &t, int *n_frames) {
     for (int i = 0; i < (int)order.size(); ++i) {
         const SlotRef &r = t.slots[order[i]];
         const bool ext = r.s->slots[r.slot].external;
-        if (!in_runs.empty() && !ext && neighbours(i - 1, i) && !t.slots[order[i - 1]].s->slots[t.slots[order[i - 1]].slot].external && in_runs.back().last == i - 1) in_runs.back().last = i;
+        const int lim = c->run_limit > 0 ? c->run_limit : (int)order.size();
+        if (!in_runs.empty() && !ext && neighbours(i - 1, i) && !t.slots[order[i - 1]].s->slots[t.slots[order[i - 1]].slot].external &&
+            in_runs.back().last == i - 1 && i - in_runs.back().first < lim) in_runs.back().last = i;
         else in_runs.push_back(Run{i, i});
-        if (!out_runs.empty() && !r.s->padded_out && neighbours(i - 1, i) && !t.slots[order[i - 1]].s->padded_out && out_runs.back().last == i - 1) out_runs.back().last = i;
+        if (!out_runs.empty() && !r.s->padded_out && neighbours(i - 1, i) && !t.slots[order[i - 1]].s->padded_out &&
+            out_runs.back().last == i - 1 && i - out_runs.back().first < lim) out_runs.back().last = i;
         else out_runs.push_back(Run{i, i});
     }
     // 2. H2D, one copy per run on the input stream of the run's first camera

@@ -306,6 +306,10 @@ class FramePath:
         """Helper threads that share the staging copy of large (4K) frames with the submitting thread."""
         check(self._L.vep_set_staging_threads(self._ctx, int(n)), "vep_set_staging_threads")
 
+    def set_copy_run_limit(self, max_frames_per_copy: int):
+        """Most frames a merged copy of neighbouring cameras may carry (0: no limit, 1: one copy per frame)."""
+        check(self._L.vep_set_copy_run_limit(self._ctx, int(max_frames_per_copy)), "vep_set_copy_run_limit")
+
     def tick_begin(self) -> int:
         n = C.c_int()
         check(self._L.vep_tick_begin(self._ctx, C.byref(n)), "vep_tick_begin")
