@@ -183,7 +183,8 @@ int vep_stream_close(vep_ctx *ctx, int stream_id);
 /* Helper threads for the staging copy (default 0).  One core copies 10-16 GB/s into pinned memory, a PCIe Gen5
  * link takes 55.  vep_submit: frames of 4 MB and more (4K) are cut into pieces copied by the submitting thread and
  * the helpers; smaller frames are copied by the submitting thread alone (one producer thread per camera already
- * covers them, as the reference's one process per camera does).  vep_submit_batch: all pieces of all frames. */
+ * covers them, as the reference's one process per camera does).  vep_submit_batch: all pieces of all frames.
+ * Change the count only while no vep_submit / vep_submit_batch call is in progress. */
 int vep_set_staging_threads(vep_ctx *ctx, int n);
 
 /* Hand one decoded frame (HOST pointers: AVFrame planes + linesizes) to the library.  `convert` is

@@ -1215,8 +1215,9 @@ static int tick_enqueue(vep_ctx *c, TickRec &t, int *n_frames) {
     return VEP_OK;
 }
 
-// Retire ticks, oldest first, up to and including `upto` (UINT64_MAX: only the oldest one).  The event waits run
-// without the context lock, so producers keep staging and other threads keep beginning ticks meanwhile.
+// Retire ticks, oldest first: only the oldest one (only_oldest), or all up to and including ticket `upto`.  The event
+// waits run without the context lock, so producers keep staging and other threads keep beginning ticks meanwhile;
+// when two threads wait for the same tick, the one that finds it already retired simply moves on.
 static int retire_ticks(vep_ctx *c, uint64_t upto, bool only_oldest) {
     DeviceGuard g(c->device);
     for (;;) {
