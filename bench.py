@@ -63,7 +63,7 @@ WORKLOADS = {
     "1x480p": (1, "yuv420p", 640, 480, "one 640x480 yuv420p stream (BASELINE configs[0])"),
     "16x854x480": (16, "yuv420p", 854, 480, "16 synthetic 854x480 yuv420p cameras per GPU: width not a multiple of 16 (rows padded to 16-byte strides, partial last lane)"),
     "16x1366x768": (16, "yuv420p", 1366, 768, "16 synthetic 1366x768 yuv420p cameras per GPU: width not a multiple of 16 (rows padded to 16-byte strides, partial last lane)"),
-    "16x854x480-tight": (16, "yuv420p", 854, 480, "16 synthetic 854x480 yuv420p cameras per GPU in TIGHT device buffers (stride = width): the scalar kernel path"),
+    "16x854x480-tight": (16, "yuv420p", 854, 480, "16 synthetic 854x480 yuv420p cameras per GPU in TIGHT device buffers (stride = width, rows at every alignment): loads and stores assembled from aligned chunks"),
 }
 MIXED_SIZES = [(640, 480)] * 43 + [(1280, 720)] * 43 + [(1920, 1080)] * 42
 

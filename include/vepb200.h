@@ -54,12 +54,14 @@ typedef enum {
  * Takes the place of one `frame.to_ndarray(format='bgr24')` call (read_image.py:94):
  * plane[]/stride[] are the AVFrame planes and linesizes, dst is the (H, W, 3) uint8 result
  * (dst_stride = 3*width for the contiguous array PyAV returns after its padding strip).
- * Any even geometry and any alignment is accepted and gives the same bytes.  The fast (vector) path needs
- * 16-byte aligned plane and dst pointers and strides that are multiples of 16 (planar 8-bit chroma: 8); for
- * 8-bit formats the width itself may be any even number.  With such strides and a width that is not a multiple
- * of 16 the kernel READS up to 15 bytes of padding behind the visible samples of a row (as libswscale does with
- * an AVFrame's padded linesize) — every row, the last one included, must therefore have `stride` readable bytes;
- * nothing outside the visible 3*width bytes of an output row is ever written. */
+ * Any even geometry and any alignment is accepted and gives the same bytes.  Fastest: 16-byte aligned plane and dst
+ * pointers and strides that are multiples of 16 (planar 8-bit chroma: 8), any even width (what an AVFrame's padded
+ * linesizes give, and what the host pipeline stages).  8-bit 4:2:0 / 4:2:2 / NV12 / NV21 frames of any other alignment
+ * (tight rows of a width like 854, odd offsets) keep the same tiling with loads and stores assembled from the aligned
+ * 16-byte chunks around them (about half the speed); 4:4:4, gray and 10-bit frames that are not aligned take a scalar
+ * path.  Loads are always whole aligned 16-byte (8-byte) chunks that contain at least one visible sample of the row, so
+ * up to 15 bytes beside a row may be READ but never a byte of an unmapped page; nothing outside the visible 3*width
+ * bytes of an output row is ever written. */
 typedef struct {
     const uint8_t *plane[3]; /* Y,U,V  (nv12/nv21: Y,UV,NULL) */
     int32_t stride[3];       /* bytes per row of each plane */

@@ -75,7 +75,7 @@ def test_seeded_random_config_sizes(path, fmt):
 
 
 @pytest.mark.parametrize("fmt", ALL_FORMATS)
-def test_ragged_geometries_take_the_generic_path(path, fmt):
+def test_ragged_geometries_in_tight_buffers(path, fmt):
     for w in (2, 6, 14, 18, 30, 34, 62, 130, 510, 514, 642, 1922):
         for h in (2, 4, 8, 10, 18, 50):
             if fmt in TALL_ONLY and h < 8:
@@ -221,6 +221,34 @@ def test_ragged_widths_on_the_vector_path(path, fmt):
                 path.convert_batch([d], torch.cuda.current_stream().cuda_stream)
                 torch.cuda.synchronize()
                 _check_padded(case)
+
+
+@pytest.mark.parametrize("fmt", ["yuv420p", "yuvj420p", "nv12", "nv21", "yuv422p", "yuvj422p"])
+def test_tight_rows_of_any_alignment_keep_the_vector_tiling(path, fmt):
+    """Contiguous tensors whose width is not a multiple of 16 (every row starts at another alignment), and planes / outputs
+    at odd byte offsets: loads and stores are assembled from the aligned chunks around them.  Oracle-exact, and nothing
+    outside the visible bytes of the output is touched."""
+    for w, h in ((854, 480), (1366, 768), (1922, 1080), (2, 8), (34, 10), (530, 8)):
+        planes = make_planes(fmt, w, h, w + h)
+        assert np.array_equal(gpu_convert(path, fmt, planes), F.to_bgr24(fmt, planes)), (fmt, w, h)
+    rng = np.random.default_rng(11)
+    for w, h, off, pad in ((640, 16, 1, 0), (640, 16, 3, 5), (854, 24, 7, 1), (1920, 8, 13, 3), (50, 10, 15, 9)):
+        planes = make_planes(fmt, w, h, off)
+        ptrs, strides, keep = [], [], []
+        for p in planes:
+            ph, pw = p.shape
+            buf = torch.from_numpy(rng.integers(0, 256, (ph * (pw + pad) + off + 64,), dtype=np.uint8)).cuda()
+            view = buf[off:off + ph * (pw + pad)].view(ph, pw + pad)
+            view[:, :pw] = torch.from_numpy(p).cuda()
+            keep.append(buf); ptrs.append(view.data_ptr()); strides.append(pw + pad)
+        dstride = 3 * w + pad
+        obuf = torch.full((h * dstride + off + 64,), 0x5A, dtype=torch.uint8, device="cuda")
+        path.convert_batch([desc_from_device_ptrs(fmt, w, h, ptrs, strides, obuf.data_ptr() + off, dstride)], torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        o = obuf.cpu().numpy()
+        rows = o[off:off + h * dstride].reshape(h, dstride)
+        assert np.array_equal(rows[:, :3 * w].reshape(h, w, 3), F.to_bgr24(fmt, planes)), (fmt, w, h, off, pad)
+        assert (rows[:, 3 * w:] == 0x5A).all() and (o[:off] == 0x5A).all() and (o[off + h * dstride:] == 0x5A).all(), (fmt, w, h, off, pad)
 
 
 def test_ragged_widths_mixed_launch_and_device_table(path):

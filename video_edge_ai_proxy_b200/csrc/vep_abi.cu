@@ -129,7 +129,11 @@ static int build_tables(const vep_frame_desc *d, int n, Tables &t) {
         const size_t ca = (nv12 || bps == 2 || vep::fmt_is_444(s.fmt)) ? 16 : 8;
         const bool vec = (bps == 1 || w % 16 == 0) && aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
                          (nv12 || gray || (aligned(f.c1, ca) && f.sc1 % ca == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
-        f.fast = vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;
+        // 8-bit 4:2:0 / 4:2:2 / NV12 / NV21 keep the vector tiling whatever the alignment (tight rows of an odd width, odd
+        // offsets): PATH_UNALIGNED assembles its loads and stores from the aligned chunks around them.  The other formats
+        // fall back to the scalar path when they are not aligned.
+        const bool any_align = bps == 1 && !gray && !vep::fmt_is_444(s.fmt);
+        f.fast = vec ? vep::PATH_VECTOR : any_align ? vep::PATH_UNALIGNED : vep::PATH_GENERIC;
         if (vep::fmt_vector_only_when_specialised(s.fmt))
             f.fast = (f.fast != vep::PATH_GENERIC && homogeneous) ? vep::PATH_VECTOR : vep::PATH_GENERIC;
         // only the tick kernel has a vector path for 4:2:2, 4:4:4, gray and for 10-bit samples
@@ -315,6 +319,7 @@ static void fill_tick(const Tables &t, std::vector<uint8_t> &blob, int wait_prio
     P->uniform_ctas = (n > 0 && n <= 65535) ? per : 0;
     int only = n ? t.frames[0].fmt : -1;
     for (int i = 1; i < n; ++i) if (t.frames[i].fmt != only) only = -1;
+    for (int i = 0; i < n; ++i) if (t.frames[i].fast == vep::PATH_UNALIGNED) only = -1;   // that code lives in the all-format kernel only
     P->only_fmt = only;        // host-side hint: all frames share one pixel format -> format-specialised kernel
     for (int i = 0; i <= n; ++i) P->cta_begin[i] = t.tick_cta_begin[i];
     for (int i = 0; i < n; ++i) P->frames[i] = t.frames[i];
@@ -1396,7 +1401,7 @@ static int noalloc_frame(const vep_frame_desc &s, int i, FrameDev &f) {
     const size_t ca = nv12 ? 16 : 8;
     const bool vec = aligned(f.y, 16) && f.sy % 16 == 0 && aligned(f.c0, ca) && f.sc0 % ca == 0 &&
                      (nv12 || gray || (aligned(f.c1, 8) && f.sc1 % 8 == 0)) && aligned(f.dst, 16) && f.sd % 16 == 0;
-    f.fast = vec ? vep::PATH_VECTOR : vep::PATH_GENERIC;   // the table-driven kernel knows these two paths
+    f.fast = vec ? vep::PATH_VECTOR : vep::PATH_UNALIGNED;   // the table-driven kernel: aligned, or assembled from aligned chunks
     if (vep::fmt_is_422(s.fmt) || vep::fmt_vector_only_when_specialised(s.fmt) || bps == 2) f.fast = vep::PATH_GENERIC;   // ... 4:2:2 / 4:4:4 / gray / 10-bit on the scalar one
     f.fast_tbl = f.fast;
     f.segs = (w + vep::kSegPx - 1) / vep::kSegPx;

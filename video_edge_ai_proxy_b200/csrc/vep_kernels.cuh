@@ -46,7 +46,7 @@ __host__ __device__ constexpr bool fmt_vector_only_when_specialised(int f) { ret
 __host__ __device__ constexpr bool fmt_is_full_range(int f) { return f == FMT_YUVJ420P || f == FMT_YUVJ422P || f == FMT_YUVJ444P; }
 __host__ __device__ constexpr int fmt_bytes_per_sample(int f) { return f == FMT_YUV420P10 ? 2 : 1; }
 
-enum : int { PATH_GENERIC = 0, PATH_VECTOR = 1 };
+enum : int { PATH_GENERIC = 0, PATH_VECTOR = 1, PATH_UNALIGNED = 2 };
 
 struct __align__(16) FrameDev {   // 80 bytes, one per converted frame (+1 sentinel), lives in device memory
     const uint8_t *y, *c0, *c1;   // Y, U|UV, V
@@ -55,7 +55,9 @@ struct __align__(16) FrameDev {   // 80 bytes, one per converted frame (+1 senti
     int32_t w, h;
     int32_t fmt;
     int32_t fast;                 // PATH_*: 0 scalar (any even geometry, any alignment), 1 vector (16-byte aligned
-                                  //         planes and strides; any even width)
+                                  //         planes and strides; any even width), 2 the vector tiling over planes, strides
+                                  //         and output of ANY alignment (8-bit 4:2:0 / 4:2:2 / NV12 / NV21): loads and
+                                  //         stores are assembled from the aligned 16-byte chunks around them
     int32_t item_begin;           // first work item of this frame in the launch-wide item space (sentinel: total)
     int32_t segs;                 // 512-px segments per row pair
     uint32_t segs_magic;          // ceil(2^32 / segs): rp = umulhi(local, magic) for local < 2^20
@@ -111,6 +113,39 @@ __device__ __forceinline__ uint2 ld_stream_v2(const uint8_t *p) {
 }
 __device__ __forceinline__ void st_stream_v4(uint8_t *p, const uint4 &v) {
     asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// ---- 16 / 8 bytes from ANY address (PATH_UNALIGNED).  The aligned chunk that holds the first byte is loaded, and the
+// next one only if one of the n bytes the lane needs lies in it: every chunk touched contains a byte of the plane, so no
+// load can reach an unmapped page.  Rows of a warp are 16 (8) bytes apart per lane, so `a` is warp-uniform. ----
+__device__ __forceinline__ uint4 shift_chunks16(const uint4 &lo, const uint4 &hi, uint32_t a) {   // bytes a .. a+15 of lo:hi, 0 < a < 16
+    const uint32_t sh = (a & 3u) * 8u;
+    switch (a >> 2) {
+        case 0: return make_uint4(__funnelshift_r(lo.x, lo.y, sh), __funnelshift_r(lo.y, lo.z, sh), __funnelshift_r(lo.z, lo.w, sh), __funnelshift_r(lo.w, hi.x, sh));
+        case 1: return make_uint4(__funnelshift_r(lo.y, lo.z, sh), __funnelshift_r(lo.z, lo.w, sh), __funnelshift_r(lo.w, hi.x, sh), __funnelshift_r(hi.x, hi.y, sh));
+        case 2: return make_uint4(__funnelshift_r(lo.z, lo.w, sh), __funnelshift_r(lo.w, hi.x, sh), __funnelshift_r(hi.x, hi.y, sh), __funnelshift_r(hi.y, hi.z, sh));
+        default: return make_uint4(__funnelshift_r(lo.w, hi.x, sh), __funnelshift_r(hi.x, hi.y, sh), __funnelshift_r(hi.y, hi.z, sh), __funnelshift_r(hi.z, hi.w, sh));
+    }
+}
+__device__ __forceinline__ uint4 ldg16_any(const uint8_t *p, int n) {
+    const uint32_t a = (uint32_t)(reinterpret_cast<uintptr_t>(p) & 15u);
+    const uint8_t *q = p - a;
+    const uint4 lo = __ldg(reinterpret_cast<const uint4 *>(q));      // cached: the neighbouring lane needs this chunk too
+    if (a == 0) return lo;
+    uint4 hi = make_uint4(0, 0, 0, 0);
+    if ((int)a + n > 16) hi = __ldg(reinterpret_cast<const uint4 *>(q + 16));
+    return shift_chunks16(lo, hi, a);
+}
+__device__ __forceinline__ uint2 ldg8_any(const uint8_t *p, int n) {
+    const uint32_t a = (uint32_t)(reinterpret_cast<uintptr_t>(p) & 7u);
+    const uint8_t *q = p - a;
+    const uint2 lo = __ldg(reinterpret_cast<const uint2 *>(q));
+    if (a == 0) return lo;
+    uint2 hi = make_uint2(0, 0);
+    if ((int)a + n > 8) hi = __ldg(reinterpret_cast<const uint2 *>(q + 8));
+    const uint32_t sh = (a & 3u) * 8u;
+    return (a >> 2) == 0 ? make_uint2(__funnelshift_r(lo.x, lo.y, sh), __funnelshift_r(lo.y, hi.x, sh))
+                         : make_uint2(__funnelshift_r(lo.y, hi.x, sh), __funnelshift_r(hi.x, hi.y, sh));
 }
 
 // packed saturating add: per 16-bit lane max(min(a + b, 255), 0)  (VIADDMNMX.S16x2.RELU on sm_90+)
@@ -308,11 +343,13 @@ __device__ __forceinline__ uint32_t swap_pairs(uint32_t w) { return prmt(w, 0, 0
 __device__ __forceinline__ uint4 swap_pairs(const uint4 &v) { return make_uint4(swap_pairs(v.x), swap_pairs(v.y), swap_pairs(v.z), swap_pairs(v.w)); }
 
 template <bool FULL>
-__device__ __forceinline__ void lane_planar(const FrameDev &f, int rp, int x, uint32_t (&o0)[12], uint32_t (&o1)[12]) {
-    const uint4 ya = ld_stream_v4(f.y + (size_t)(2 * rp) * f.sy + x);
-    const uint4 yb = ld_stream_v4(f.y + (size_t)(2 * rp + 1) * f.sy + x);
-    const uint2 uu = ld_stream_v2(f.c0 + (size_t)rp * f.sc0 + (x >> 1));
-    const uint2 vv = ld_stream_v2(f.c1 + (size_t)rp * f.sc1 + (x >> 1));
+__device__ __forceinline__ void lane_planar(const FrameDev &f, int rp, int x, bool un, uint32_t (&o0)[12], uint32_t (&o1)[12]) {
+    const uint8_t *py = f.y + (size_t)(2 * rp) * f.sy + x, *pu = f.c0 + (size_t)rp * f.sc0 + (x >> 1), *pv = f.c1 + (size_t)rp * f.sc1 + (x >> 1);
+    const int nb = min(16, f.w - x);                 // visible luma bytes of this lane
+    const uint4 ya = un ? ldg16_any(py, nb) : ld_stream_v4(py);
+    const uint4 yb = un ? ldg16_any(py + f.sy, nb) : ld_stream_v4(py + f.sy);
+    const uint2 uu = un ? ldg8_any(pu, nb >> 1) : ld_stream_v2(pu);
+    const uint2 vv = un ? ldg8_any(pv, nb >> 1) : ld_stream_v2(pv);
     compute_planar<FULL>(ya, yb, uu, vv, o0, o1);
 }
 
@@ -339,12 +376,14 @@ __device__ __forceinline__ void compute_nv12(const uint4 &ya, const uint4 &yb, c
         }
     }
 }
-__device__ __forceinline__ void lane_nv12(const FrameDev &f, int rp, int x, uint32_t (&o0)[12], uint32_t (&o1)[12]) {
-    const uint4 ya = ld_stream_v4(f.y + (size_t)(2 * rp) * f.sy + x);
-    const uint4 yb = ld_stream_v4(f.y + (size_t)(2 * rp + 1) * f.sy + x);
+__device__ __forceinline__ void lane_nv12(const FrameDev &f, int rp, int x, bool un, uint32_t (&o0)[12], uint32_t (&o1)[12]) {
+    const uint8_t *py = f.y + (size_t)(2 * rp) * f.sy + x;
+    const int nb = min(16, f.w - x);
+    const uint4 ya = un ? ldg16_any(py, nb) : ld_stream_v4(py);
+    const uint4 yb = un ? ldg16_any(py + f.sy, nb) : ld_stream_v4(py + f.sy);
     const int up = rp > 0 ? rp - 1 : 0;
-    uint4 cu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)rp * f.sc0 + x));   // u0 v0 u1 v1 ...
-    uint4 pu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)up * f.sc0 + x));   // row above (L2/L1 hit)
+    uint4 cu = un ? ldg16_any(f.c0 + (size_t)rp * f.sc0 + x, nb) : __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)rp * f.sc0 + x));   // u0 v0 u1 v1 ...
+    uint4 pu = un ? ldg16_any(f.c0 + (size_t)up * f.sc0 + x, nb) : __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)up * f.sc0 + x));   // row above (L2/L1 hit)
     if (f.fmt == FMT_NV21) { cu = swap_pairs(cu); pu = swap_pairs(pu); }
     compute_nv12(ya, yb, cu, pu, rp == (f.h >> 1) - 1, o0, o1);   // rows H-2, H-1: swscale leaves its SIMD output stage
 }
@@ -474,6 +513,26 @@ __device__ __forceinline__ void store_segment(uint8_t *g, const uint8_t *t, int 
     }
 }
 
+// The same for a row that starts at ANY address (PATH_UNALIGNED): the aligned 16-byte chunks of the OUTPUT are assembled
+// from the two tile chunks each straddles (tile rows are 16-byte aligned and 1536 bytes long: the second chunk of a
+// fully covered output chunk always lies inside the row); the partial chunks at both ends leave as byte stores.
+__device__ __forceinline__ void store_segment_any(uint8_t *g, const uint8_t *t, int seg_bytes, int lane) {
+    const uint32_t a = (uint32_t)(reinterpret_cast<uintptr_t>(g) & 15u);
+    if (a == 0) { store_segment(g, t, seg_bytes, lane); return; }   // warp-uniform
+    uint8_t *G = g - a;                                              // first aligned chunk that holds a byte of the row
+    const int nch = ((int)a + seg_bytes + 15) >> 4;
+    for (int k = lane; k < nch; k += 32) {
+        const int o = 16 * k - (int)a;                               // tile offset of the chunk's first byte
+        if (o >= 0 && o + 16 <= seg_bytes) {
+            const int r = o & 15;                                    // = 16 - a
+            const uint4 lo = *reinterpret_cast<const uint4 *>(t + (o - r)), hi = *reinterpret_cast<const uint4 *>(t + (o - r) + 16);
+            st_stream_v4(G + 16 * k, shift_chunks16(lo, hi, (uint32_t)r));
+        } else {
+            for (int b = max(o, 0); b < min(o + 16, seg_bytes); ++b) g[b] = t[b];
+        }
+    }
+}
+
 // ---- the table-driven kernel -----------------------------------------------------------------------
 // Descriptor tables in device memory (FrameDev[], CtaWork[]): the path for more than 128 frames per launch
 // and for vep_convert_batch_noalloc.  One warp item = 512 px x 2 luma rows; shared-memory re-order, then
@@ -500,10 +559,11 @@ yuv_to_bgr24_batched(const FrameDev *__restrict__ frames, const CtaWork *__restr
 
     uint32_t o0[12], o1[12];
     const bool active = x < f.w;             // the last active lane of a row may cover fewer than 16 visible pixels
+    const bool un = f.fast_tbl == PATH_UNALIGNED;
     if (active) {
-        if (f.fmt == FMT_YUV420P) lane_planar<false>(f, rp, x, o0, o1);
-        else if (f.fmt == FMT_YUVJ420P) lane_planar<true>(f, rp, x, o0, o1);
-        else lane_nv12(f, rp, x, o0, o1);   // nv12 / nv21 (other formats never reach here: fast_tbl is generic)
+        if (f.fmt == FMT_YUV420P) lane_planar<false>(f, rp, x, un, o0, o1);
+        else if (f.fmt == FMT_YUVJ420P) lane_planar<true>(f, rp, x, un, o0, o1);
+        else lane_nv12(f, rp, x, un, o0, o1);   // nv12 / nv21 (other formats never reach here: fast_tbl is generic)
     }
     uint8_t *g0 = f.dst + (size_t)(2 * rp) * f.sd + (size_t)seg * kSegBytes;
     const int seg_bytes = min(kSegPx, f.w - seg * kSegPx) * 3;
@@ -517,8 +577,8 @@ yuv_to_bgr24_batched(const FrameDev *__restrict__ frames, const CtaWork *__restr
         }
     }
     __syncwarp();
-    store_segment(g0, t0, seg_bytes, lane);
-    store_segment(g0 + f.sd, t1, seg_bytes, lane);
+    if (un) { store_segment_any(g0, t0, seg_bytes, lane); store_segment_any(g0 + f.sd, t1, seg_bytes, lane); }
+    else { store_segment(g0, t0, seg_bytes, lane); store_segment(g0 + f.sd, t1, seg_bytes, lane); }
 }
 
 
@@ -597,21 +657,31 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     const bool nv12 = fmt_is_semiplanar(fmt);
     const bool p10 = fmt == FMT_YUV420P10;               // 16-bit containers: loaded per row pair below, not here
     const int cshift = fmt_is_422(fmt) ? 1 : 0;           // 4:2:2: chroma row of luma row j is row j, not j/2
+    // planes, strides or output of any alignment: only the all-format instantiation carries this code (the host sends
+    // launches with such frames there), so the per-format kernels stay as they are
+    const bool un = ONLY < 0 && f.fast == PATH_UNALIGNED;
+    const int nb = min(16, f.w - x);                      // visible luma bytes of this lane
     if (active && !p10 && !fmt_vector_only_when_specialised(fmt)) {
 #pragma unroll
         for (int r = 0; r < RPT; ++r) {
             const int rp = min(rp0 + r, hp - 1);            // clamp: an odd tail group re-reads the last pair (not stored)
-            ya[r] = ld_stream_v4(f.y + (size_t)(2 * rp) * f.sy + x);
-            yb[r] = ld_stream_v4(f.y + (size_t)(2 * rp + 1) * f.sy + x);
+            const uint8_t *py = f.y + (size_t)(2 * rp) * f.sy + x;
+            ya[r] = un ? ldg16_any(py, nb) : ld_stream_v4(py);
+            yb[r] = un ? ldg16_any(py + f.sy, nb) : ld_stream_v4(py + f.sy);
             if (nv12) {
-                ca[r] = ld_stream_v4(f.c0 + (size_t)rp * f.sc0 + x);
+                const uint8_t *pc = f.c0 + (size_t)rp * f.sc0 + x;
+                ca[r] = un ? ldg16_any(pc, nb) : ld_stream_v4(pc);
             } else {
-                const uint2 uu = ld_stream_v2(f.c0 + (size_t)(rp << cshift) * f.sc0 + (x >> 1));
-                const uint2 vv = ld_stream_v2(f.c1 + (size_t)(rp << cshift) * f.sc1 + (x >> 1));
+                const uint8_t *pcu = f.c0 + (size_t)(rp << cshift) * f.sc0 + (x >> 1), *pcv = f.c1 + (size_t)(rp << cshift) * f.sc1 + (x >> 1);
+                const uint2 uu = un ? ldg8_any(pcu, nb >> 1) : ld_stream_v2(pcu);
+                const uint2 vv = un ? ldg8_any(pcv, nb >> 1) : ld_stream_v2(pcv);
                 ca[r] = make_uint4(uu.x, uu.y, vv.x, vv.y);
             }
         }
-        if (nv12) pu = __ldg(reinterpret_cast<const uint4 *>(f.c0 + (size_t)(rp0 > 0 ? rp0 - 1 : 0) * f.sc0 + x));
+        if (nv12) {
+            const uint8_t *pp = f.c0 + (size_t)(rp0 > 0 ? rp0 - 1 : 0) * f.sc0 + x;
+            pu = un ? ldg16_any(pp, nb) : __ldg(reinterpret_cast<const uint4 *>(pp));
+        }
         if (fmt == FMT_NV21) {                            // V first: swap each pair once, then it is NV12
             pu = swap_pairs(pu);
 #pragma unroll
@@ -673,8 +743,9 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
             else compute_planar_row<true>(ya[r], make_uint2(ca[r].x, ca[r].y), make_uint2(ca[r].z, ca[r].w), o);
 #pragma unroll
             for (int k = 0; k < 3; ++k) *reinterpret_cast<uint4 *>(t0 + lane * 48 + k * 16) = make_uint4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
-            const uint2 ub = ld_stream_v2(f.c0 + (size_t)(2 * rp + 1) * f.sc0 + (x >> 1));
-            const uint2 vb = ld_stream_v2(f.c1 + (size_t)(2 * rp + 1) * f.sc1 + (x >> 1));
+            const uint8_t *pub = f.c0 + (size_t)(2 * rp + 1) * f.sc0 + (x >> 1), *pvb = f.c1 + (size_t)(2 * rp + 1) * f.sc1 + (x >> 1);
+            const uint2 ub = un ? ldg8_any(pub, nb >> 1) : ld_stream_v2(pub);
+            const uint2 vb = un ? ldg8_any(pvb, nb >> 1) : ld_stream_v2(pvb);
             if (fmt == FMT_YUV422P) compute_planar_row<false>(yb[r], ub, vb, o);
             else compute_planar_row<true>(yb[r], ub, vb, o);
 #pragma unroll
@@ -695,8 +766,8 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
         // writes must be complete before ours land (same output buffer re-used by consecutive launches)
         if (p.wait_prior == 2 && r == 0) asm volatile("griddepcontrol.wait;" ::: "memory");
         uint8_t *g0 = f.dst + (size_t)(2 * rp) * f.sd + (size_t)seg * kSegBytes;
-        store_segment(g0, t0, seg_bytes, lane);
-        store_segment(g0 + f.sd, t1, seg_bytes, lane);
+        if (un) { store_segment_any(g0, t0, seg_bytes, lane); store_segment_any(g0 + f.sd, t1, seg_bytes, lane); }
+        else { store_segment(g0, t0, seg_bytes, lane); store_segment(g0 + f.sd, t1, seg_bytes, lane); }
         if (RPT > 1) __syncwarp();                          // tile is re-used by the next row pair
     }
 }

@@ -14,6 +14,7 @@ All arithmetic runs in libvepb200.so's sm_100a kernels; nothing here converts pi
 from __future__ import annotations
 
 import ctypes as C
+import threading
 from typing import Dict, Optional, Sequence
 
 import numpy as np
@@ -150,6 +151,7 @@ class FramePath:
         self._ids: Dict[str, int] = {}
         self._geom: Dict[str, tuple] = {}
         self._next_id = 0
+        self._open_lock = threading.Lock()      # stream ids are handed out here: cameras may be opened from several threads
 
     # ---- lifecycle -----------------------------------------------------------------------------
     def close(self):
@@ -176,16 +178,23 @@ class FramePath:
             raise VepError(_abi.VEP_ERR_STATE, "open_stream", f"{device_id!r} already open")
         if fmt not in VEP_FMT:
             raise VepError(_abi.VEP_ERR_INVALID_ARG, "open_stream", f"unknown format {fmt!r}")
-        sid = self._next_id
-        check(self._L.vep_stream_open(self._ctx, sid, VEP_FMT[fmt], width, height, memory_buffer), "vep_stream_open")
-        self._next_id += 1
-        self._ids[device_id] = sid
-        self._geom[device_id] = (fmt, width, height)
+        with self._open_lock:
+            if device_id in self._ids:
+                raise VepError(_abi.VEP_ERR_STATE, "open_stream", f"{device_id!r} already open")
+            sid = self._next_id
+            check(self._L.vep_stream_open(self._ctx, sid, VEP_FMT[fmt], width, height, memory_buffer), "vep_stream_open")
+            self._next_id += 1
+            self._ids[device_id] = sid
+            self._geom[device_id] = (fmt, width, height)
 
     def open_streams(self, cameras, memory_buffer: int = 1):
         """Declare several cameras at once: `cameras` = [(device_id, fmt, width, height), ...].  Their slots share one
         allocation laid out [slot][camera], so cameras that are neighbours in the list and tick in lock step are copied to
         and from the GPU with one copy per direction for the whole run (vep_stream_open_many)."""
+        with self._open_lock:
+            self._open_streams_locked(cameras, memory_buffer)
+
+    def _open_streams_locked(self, cameras, memory_buffer):
         specs = (_abi.StreamSpec * len(cameras))()
         for i, (device_id, fmt, w, h) in enumerate(cameras):
             if device_id in self._ids or device_id in [c[0] for c in cameras[:i]]:
@@ -200,8 +209,9 @@ class FramePath:
         self._next_id += len(cameras)
 
     def close_stream(self, device_id: str):
-        check(self._L.vep_stream_close(self._ctx, self._sid(device_id)), "vep_stream_close")
-        del self._ids[device_id], self._geom[device_id]
+        with self._open_lock:
+            check(self._L.vep_stream_close(self._ctx, self._sid(device_id)), "vep_stream_close")
+            del self._ids[device_id], self._geom[device_id]
 
     def _sid(self, device_id: str) -> int:
         try:
