@@ -306,6 +306,7 @@ struct DeviceGuard {
 
 // ---- tick kernel: descriptor table travels as a kernel parameter -------------------------------------
 static constexpr int kTickCapSmall = 16, kTickCapLarge = 128;
+static constexpr int kOnlyFmtUnaligned = 0x100;   // flag in TickParams::only_fmt (host side only)
 
 template <int NF>
 static void fill_tick(const Tables &t, std::vector<uint8_t> &blob, int wait_prior) {
@@ -319,8 +320,11 @@ static void fill_tick(const Tables &t, std::vector<uint8_t> &blob, int wait_prio
     P->uniform_ctas = (n > 0 && n <= 65535) ? per : 0;
     int only = n ? t.frames[0].fmt : -1;
     for (int i = 1; i < n; ++i) if (t.frames[i].fmt != only) only = -1;
-    for (int i = 0; i < n; ++i) if (t.frames[i].fast == vep::PATH_UNALIGNED) only = -1;   // that code lives in the all-format kernel only
-    P->only_fmt = only;        // host-side hint: all frames share one pixel format -> format-specialised kernel
+    bool any_unaligned = false;
+    for (int i = 0; i < n; ++i) any_unaligned |= t.frames[i].fast == vep::PATH_UNALIGNED;
+    // host-side hint: all frames share one pixel format -> format-specialised kernel; bit 8: some frame needs the
+    // any-alignment loads and stores -> the flavour of that kernel which carries them
+    P->only_fmt = only < 0 ? -1 : (only | (any_unaligned ? kOnlyFmtUnaligned : 0));
     for (int i = 0; i <= n; ++i) P->cta_begin[i] = t.tick_cta_begin[i];
     for (int i = 0; i < n; ++i) P->frames[i] = t.frames[i];
 }
@@ -338,6 +342,17 @@ static int make_tick_blob(const Tables &t, std::vector<uint8_t> &blob, int *grid
 template <int NF>
 static const void *tick_kernel(int only_fmt) {
     constexpr int R = vep::kTickRpt;
+    if (only_fmt >= 0 && (only_fmt & kOnlyFmtUnaligned)) {
+        switch (only_fmt & 0xff) {
+            case VEP_FMT_YUV420P: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_YUV420P, true>;
+            case VEP_FMT_YUVJ420P: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_YUVJ420P, true>;
+            case VEP_FMT_NV12: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_NV12, true>;
+            case VEP_FMT_NV21: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_NV21, true>;
+            case VEP_FMT_YUV422P: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_YUV422P, true>;
+            case VEP_FMT_YUVJ422P: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_YUVJ422P, true>;
+            default: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4>;   // cannot happen: other formats are never PATH_UNALIGNED
+        }
+    }
     switch (only_fmt) {
         case VEP_FMT_YUV420P: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_YUV420P>;
         case VEP_FMT_YUVJ420P: return (const void *)vep::yuv_to_bgr24_tick<NF, R, 4, vep::FMT_YUVJ420P>;

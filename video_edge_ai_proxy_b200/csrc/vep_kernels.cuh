@@ -527,10 +527,14 @@ __device__ __forceinline__ void store_segment_any(uint8_t *g, const uint8_t *t, 
             const int r = o & 15;                                    // = 16 - a
             const uint4 lo = *reinterpret_cast<const uint4 *>(t + (o - r)), hi = *reinterpret_cast<const uint4 *>(t + (o - r) + 16);
             st_stream_v4(G + 16 * k, shift_chunks16(lo, hi, (uint32_t)r));
-        } else {
-            for (int b = max(o, 0); b < min(o + 16, seg_bytes); ++b) g[b] = t[b];
         }
     }
+    // the partial chunks at the two ends of the row: one byte per lane, one store request each
+    const int head = min(16 - (int)a, seg_bytes);                    // tile bytes [0, head) share the first output chunk
+    if (lane < head) g[lane] = t[lane];
+    const int tail0 = ((int)a + seg_bytes) & ~15;                    // row-relative (from G) start of the last chunk
+    const int tb = tail0 - (int)a + lane;                            // tile byte this lane would carry
+    if (tail0 > 0 && tb >= head && tb < seg_bytes && (((int)a + seg_bytes) & 15) != 0) g[tb] = t[tb];
 }
 
 // ---- the table-driven kernel -----------------------------------------------------------------------
@@ -608,7 +612,9 @@ struct TickParams {
 
 // ONLY >= 0: every frame of the launch has pixel format ONLY (a homogeneous fleet, the common case) and the other
 // formats' code is compiled out: a third of the instruction footprint, fewer instruction-cache misses.
-template <int NF, int RPT, int MINB, int ONLY = -1>
+// UN: the instantiation also carries the any-alignment loads and stores (PATH_UNALIGNED frames); the all-format kernel
+// (ONLY < 0) always does, the per-format kernels exist in both flavours so that the aligned ones stay lean.
+template <int NF, int RPT, int MINB, int ONLY = -1, bool UN = false>
 __global__ void __launch_bounds__(kThreads, MINB)
 yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     __shared__ __align__(128) uint8_t tile[kWarpsPerCta][2][kSegBytes];
@@ -657,9 +663,9 @@ yuv_to_bgr24_tick(const __grid_constant__ TickParams<NF> p) {
     const bool nv12 = fmt_is_semiplanar(fmt);
     const bool p10 = fmt == FMT_YUV420P10;               // 16-bit containers: loaded per row pair below, not here
     const int cshift = fmt_is_422(fmt) ? 1 : 0;           // 4:2:2: chroma row of luma row j is row j, not j/2
-    // planes, strides or output of any alignment: only the all-format instantiation carries this code (the host sends
-    // launches with such frames there), so the per-format kernels stay as they are
-    const bool un = ONLY < 0 && f.fast == PATH_UNALIGNED;
+    // planes, strides or output of any alignment (the host sends launches with such frames to an instantiation that
+    // carries this code)
+    const bool un = (ONLY < 0 || UN) && f.fast == PATH_UNALIGNED;
     const int nb = min(16, f.w - x);                      // visible luma bytes of this lane
     if (active && !p10 && !fmt_vector_only_when_specialised(fmt)) {
 #pragma unroll
