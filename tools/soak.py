@@ -1,6 +1,6 @@
 """Soak: many ticks, streams opened and closed, plans created and destroyed — device/host memory must not grow and
 results must stay exact.  usage: soak.py [seconds]"""
-import os, sys, time, resource
+import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 from oracle import formulas as F
