@@ -11,7 +11,7 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def test_c_program_roundtrip(tmp_path):
+def _build_and_run(tmp_path, name, marker):
     import torch
     if not torch.cuda.is_available():
         pytest.fail("marked gpu but no CUDA device")
@@ -22,10 +22,20 @@ def test_c_program_roundtrip(tmp_path):
     port.build()
     lib_dir = os.path.join(ROOT, "video_edge_ai_proxy_b200")
     ora_dir = os.path.join(ROOT, "oracle", "_build")
-    exe = str(tmp_path / "abi_roundtrip")
+    exe = str(tmp_path / name)
     subprocess.check_call([gcc, "-std=c99", "-O1", "-Wall", "-I", os.path.join(ROOT, "include"),
-                           os.path.join(ROOT, "tests", "c", "abi_roundtrip.c"), "-o", exe,
+                           os.path.join(ROOT, "tests", "c", name + ".c"), "-o", exe,
                            "-L", lib_dir, "-lvepb200", "-L", ora_dir, "-lyuv2bgr_port",
                            f"-Wl,-rpath,{lib_dir}", f"-Wl,-rpath,{ora_dir}"])
     out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
-    assert out.returncode == 0 and "C_ABI_ROUNDTRIP_OK" in out.stdout, out.stdout + out.stderr
+    assert out.returncode == 0 and marker in out.stdout, out.stdout + out.stderr
+
+
+def test_c_program_roundtrip(tmp_path):
+    _build_and_run(tmp_path, "abi_roundtrip", "C_ABI_ROUNDTRIP_OK")
+
+
+def test_c_program_batch_tickets_pinned_pool_and_slots(tmp_path):
+    """The round-2 entry points from plain C: vep_stream_open_many, vep_submit_batch + helper threads, ticketed ticks,
+    vep_host_register + VEP_SUBMIT_PINNED, vep_acquire_input / vep_commit_input."""
+    _build_and_run(tmp_path, "abi_batch", "C_ABI_BATCH_OK")
